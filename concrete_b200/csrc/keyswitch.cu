@@ -1,0 +1,245 @@
+// keyswitch.cu — K1: batched LWE keyswitch, bit-exact in wrapping u64.
+//
+// Replaces third_party/tfhe-rs/backends/tfhe-cuda-backend/cuda/src/crypto/keyswitch.cuh:42-124
+// (one block row per sample, KSK re-read per sample) and computes exactly what
+// tfhe/src/core_crypto/algorithms/lwe_keyswitch.rs:138-228 computes:
+//   out = (0,..,0,b) - sum_i sum_j digit_j(a_i) * KSK[i][j][.]
+// with closest_representable (commons/math/decomposition/decomposer.rs:23-47) and the balanced
+// signed digits of commons/math/decomposition/iter.rs:121-133 (level l first).
+//
+// Design (B200): the sum is an integer GEMM  C[s][o] = sum_kappa D[s][kappa] * KSK[kappa][o],
+// kappa = i*l + j, tiled BS samples x BO outputs per CTA so that each KSK tile is read once per
+// 128 samples instead of once per sample.  Digits are produced on the fly while staging the
+// ciphertext tile into shared memory (no digit buffer in HBM).  Digits are stored with an offset
+// d' = d + B/2 >= 0 so the 64x32 multiply-accumulate is two IMADs (IMAD.WIDE.U32 + IMAD); the
+// offset is removed at the end with the per-column sum of the KSK tile rows, accumulated on the
+// otherwise idle integer-add pipe.  Wrapping u64 addition is associative and commutative, so any
+// summation order (incl. the split-K atomics used for small batches) is bit-exact.
+#include "common.cuh"
+#include "../../include/concrete_b200.h"
+
+namespace {
+
+constexpr int BS = 128; // samples per CTA tile
+constexpr int BO = 64;  // outputs per CTA tile
+constexpr int TS = 8;   // samples per thread
+constexpr int TO = 4;   // outputs per thread
+constexpr int NT = (BS / TS) * (BO / TO); // 256 threads
+constexpr int MAX_KT = 48;                // max kappa rows per tile
+
+__device__ __forceinline__ u64 closest_representable(u64 x, u32 base_log, u32 level) {
+  const u32 shift = 64 - level * base_log - 1;
+  u64 r = x >> shift;
+  r += 1;
+  r &= ~(u64)1;
+  return r << shift;
+}
+
+__device__ __forceinline__ u64 decompose_one_level(u64 &state, u64 mask, u32 base_log) {
+  u64 res = state & mask;
+  state >>= base_log;
+  u64 carry = ((res - 1) | state) & res;
+  carry >>= (base_log - 1);
+  state += carry;
+  return res - (carry << base_log);
+}
+
+__global__ void ks_init_out(u64 *__restrict__ out, const u64 *__restrict__ out_idx,
+                            const u64 *__restrict__ in, const u64 *__restrict__ in_idx,
+                            u32 n_in, u32 n_out, u32 num_samples) {
+  const u32 s = blockIdx.y;
+  if (s >= num_samples) return;
+  u64 *row = out + out_idx[s] * (u64)(n_out + 1);
+  for (u32 o = blockIdx.x * blockDim.x + threadIdx.x; o <= n_out; o += gridDim.x * blockDim.x)
+    row[o] = (o == n_out) ? in[in_idx[s] * (u64)(n_in + 1) + n_in] : 0;
+}
+
+// grid: (ceil((n_out+1)/BO), ceil(num_samples/BS), ksplit)
+__global__ void __launch_bounds__(NT, 2)
+ks_kernel(u64 *__restrict__ out, const u64 *__restrict__ out_idx, const u64 *__restrict__ in,
+          const u64 *__restrict__ in_idx, const u64 *__restrict__ ksk, u32 n_in, u32 n_out,
+          u32 base_log, u32 level, u32 num_samples, u32 KI /* inputs per tile */,
+          u32 tiles_per_split, bool use_atomics) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const u32 KT = KI * level;                                   // kappa rows per tile
+  u32 *sD = reinterpret_cast<u32 *>(smem_raw);                 // [KT][BS]
+  u64 *sK = reinterpret_cast<u64 *>(smem_raw + (size_t)KT * BS * 4); // [KT][BO]
+  __shared__ u64 s_in_row[BS];                                 // row offsets of the CTA's samples
+
+  const u32 tid = threadIdx.x;
+  const u32 tx = tid % (BO / TO), ty = tid / (BO / TO);
+  const u32 o0 = blockIdx.x * BO, s0 = blockIdx.y * BS;
+  const u32 out_size = n_out + 1;
+
+  for (u32 x = tid; x < BS; x += NT) {
+    u32 s = s0 + x;
+    s_in_row[x] = (s < num_samples) ? in_idx[s] * (u64)(n_in + 1) : ~(u64)0;
+  }
+  __syncthreads();
+
+  const u32 num_tiles = (n_in + KI - 1) / KI;
+  const u32 tile_begin = blockIdx.z * tiles_per_split;
+  const u32 tile_end = min(num_tiles, tile_begin + tiles_per_split);
+
+  const u64 mask = ((u64)1 << base_log) - 1;
+  const u32 half_b = 1u << (base_log - 1);
+  const u32 state_shift = 64 - base_log * level;
+
+  // register staging (prefetch of the next tile)
+  constexpr int D_PER_T = 4;   // BS*KI/NT  with KI <= 8
+  constexpr int K_PER_T = MAX_KT * BO / NT; // 16
+  u64 rA[D_PER_T];
+  u64 rK[K_PER_T];
+
+  auto prefetch = [&](u32 tile) {
+    const u32 i0 = tile * KI;
+#pragma unroll
+    for (int e = 0; e < D_PER_T; ++e) {
+      u32 lin = tid + e * NT; // over BS*KI, ii fastest
+      u32 ii = lin % KI, sl = lin / KI;
+      u64 v = 0;
+      if (lin < BS * KI && i0 + ii < n_in && s_in_row[sl] != ~(u64)0)
+        v = in[s_in_row[sl] + i0 + ii];
+      rA[e] = v;
+    }
+#pragma unroll
+    for (int e = 0; e < K_PER_T; ++e) {
+      u32 lin = tid + e * NT; // over KT*BO, o fastest
+      u32 oo = lin % BO, kk = lin / BO;
+      u64 v = 0;
+      u32 ii = kk / level;
+      if (kk < KT && i0 + ii < n_in && o0 + oo < out_size)
+        v = ksk[((u64)i0 * level + kk) * out_size + o0 + oo];
+      rK[e] = v;
+    }
+  };
+
+  auto stage = [&]() {
+#pragma unroll
+    for (int e = 0; e < D_PER_T; ++e) {
+      u32 lin = tid + e * NT;
+      if (lin < BS * KI) {
+        u32 ii = lin % KI, sl = lin / KI;
+        u64 state = closest_representable(rA[e], base_log, level) >> state_shift;
+        for (u32 j = 0; j < level; ++j) {
+          u64 d = decompose_one_level(state, mask, base_log);
+          sD[(ii * level + j) * BS + sl] = (u32)d + half_b; // d' = d + B/2 in [0, B]
+        }
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < K_PER_T; ++e) {
+      u32 lin = tid + e * NT;
+      if (lin < KT * BO) sK[lin] = rK[e];
+    }
+  };
+
+  u64 acc[TS][TO];
+  u64 colsum[TO];
+#pragma unroll
+  for (int a = 0; a < TS; ++a)
+#pragma unroll
+    for (int b = 0; b < TO; ++b) acc[a][b] = 0;
+#pragma unroll
+  for (int b = 0; b < TO; ++b) colsum[b] = 0;
+
+  if (tile_begin < tile_end) prefetch(tile_begin);
+  for (u32 tile = tile_begin; tile < tile_end; ++tile) {
+    stage();
+    __syncthreads();
+    if (tile + 1 < tile_end) prefetch(tile + 1);
+#pragma unroll 4
+    for (u32 kk = 0; kk < KT; ++kk) {
+      // thread outputs: o = 2*tx + {0,1} + 32*c, c in {0,1}; samples ty*TS .. +7
+      const uint4 d0 = *reinterpret_cast<const uint4 *>(&sD[kk * BS + ty * TS]);
+      const uint4 d1 = *reinterpret_cast<const uint4 *>(&sD[kk * BS + ty * TS + 4]);
+      const ulonglong2 k0 = *reinterpret_cast<const ulonglong2 *>(&sK[kk * BO + 2 * tx]);
+      const ulonglong2 k1 = *reinterpret_cast<const ulonglong2 *>(&sK[kk * BO + 2 * tx + 32]);
+      const u32 d[TS] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+      const u64 kv[TO] = {k0.x, k0.y, k1.x, k1.y};
+#pragma unroll
+      for (int b = 0; b < TO; ++b) {
+        colsum[b] += kv[b];
+        const u32 klo = (u32)kv[b], khi = (u32)(kv[b] >> 32);
+#pragma unroll
+        for (int a = 0; a < TS; ++a)
+          acc[a][b] += (u64)klo * d[a] + ((u64)(khi * d[a]) << 32);
+      }
+    }
+    __syncthreads();
+  }
+
+  // epilogue: out = body*[o==n_out] - acc + (B/2)*colsum
+#pragma unroll
+  for (int a = 0; a < TS; ++a) {
+    const u32 sl = ty * TS + a, s = s0 + sl;
+    if (s >= num_samples) continue;
+    u64 *row = out + out_idx[s] * (u64)out_size;
+#pragma unroll
+    for (int b = 0; b < TO; ++b) {
+      const u32 o = o0 + 2 * tx + (b & 1) + 32 * (b >> 1);
+      if (o >= out_size) continue;
+      u64 v = (u64)half_b * colsum[b] - acc[a][b];
+      if (use_atomics) {
+        atomicAdd(reinterpret_cast<unsigned long long *>(&row[o]), (unsigned long long)v);
+      } else {
+        if (o == n_out) v += in[s_in_row[sl] + n_in];
+        row[o] = v;
+      }
+    }
+  }
+}
+
+} // namespace
+
+void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
+                         const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
+                         u32 level, u32 num_samples) {
+  if (num_samples == 0) return;
+  if (base_log == 0 || level == 0 || base_log * level >= 64 || base_log > 31)
+    CB_PANIC("Cuda error (keyswitch): unsupported decomposition base_log=%u level=%u", base_log,
+             level);
+  if (level > MAX_KT)
+    CB_PANIC("Cuda error (keyswitch): level_count %u > %d unsupported", level, MAX_KT);
+  u32 KI = MAX_KT / level;
+  if (KI > 8) KI = 8;
+  if (KI < 1) KI = 1;
+  const u32 KT = KI * level;
+  const u32 num_tiles = (n_in + KI - 1) / KI;
+  dim3 grid((n_out + 1 + BO - 1) / BO, (num_samples + BS - 1) / BS, 1);
+  // split-K so that small batches still fill the 148 SMs (2 CTAs/SM resident)
+  u32 ksplit = 1;
+  const u32 base_ctas = grid.x * grid.y;
+  if (base_ctas < 296) {
+    ksplit = (296 + base_ctas - 1) / base_ctas;
+    if (ksplit > num_tiles) ksplit = num_tiles;
+    if (ksplit < 1) ksplit = 1;
+  }
+  const u32 tiles_per_split = (num_tiles + ksplit - 1) / ksplit;
+  ksplit = (num_tiles + tiles_per_split - 1) / tiles_per_split;
+  grid.z = ksplit;
+  const bool use_atomics = ksplit > 1;
+  if (use_atomics) {
+    dim3 g((n_out + 1 + 255) / 256, num_samples);
+    ks_init_out<<<g, 256, 0, stream>>>(out, out_idx, in, in_idx, n_in, n_out, num_samples);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+  }
+  const size_t smem = (size_t)KT * BS * 4 + (size_t)KT * BO * 8;
+  ks_kernel<<<grid, NT, smem, stream>>>(out, out_idx, in, in_idx, ksk, n_in, n_out, base_log,
+                                        level, num_samples, KI, tiles_per_split, use_atomics);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+extern "C" void cuda_keyswitch_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, void *lwe_output_indexes,
+    void *lwe_array_in, void *lwe_input_indexes, void *ksk, uint32_t lwe_dimension_in,
+    uint32_t lwe_dimension_out, uint32_t base_log, uint32_t level_count,
+    uint32_t num_samples) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_keyswitch_launch(as_stream(stream), (u64 *)lwe_array_out, (const u64 *)lwe_output_indexes,
+                      (const u64 *)lwe_array_in, (const u64 *)lwe_input_indexes,
+                      (const u64 *)ksk, lwe_dimension_in, lwe_dimension_out, base_log,
+                      level_count, num_samples);
+}

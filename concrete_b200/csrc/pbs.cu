@@ -1,0 +1,614 @@
+// pbs.cu — K3 (fused programmable bootstrap) + K4 (BSK -> Fourier) + scratch/cleanup.
+//
+// Replaces, behind the same C ABI, the reference's classic PBS:
+//   third_party/tfhe-rs/backends/tfhe-cuda-backend/cuda/src/pbs/programmable_bootstrap_classic.cuh
+//   (DEFAULT: 2*n launches, accumulators round-trip through global memory :434-448),
+//   programmable_bootstrap_cg_classic.cuh, programmable_bootstrap_tbc_classic.cuh,
+//   programmable_bootstrap_amortized.cuh:48-213 and pbs/bootstrapping_key.cuh:75-209,
+// and computes what concrete-cpu computes:
+//   tfhe/src/core_crypto/fft_impl/fft64/crypto/bootstrap.rs:250-368  (blind rotate + extract)
+//   tfhe/src/core_crypto/fft_impl/fft64/crypto/ggsw.rs:481-602       (external product)
+//   tfhe/src/core_crypto/algorithms/glwe_sample_extraction.rs:90-165
+//
+// K3 design: ONE launch for the whole batch.  One CTA owns one ciphertext for all n CMUX
+// iterations: the GLWE accumulator stays in shared memory as (coef j, coef j+N/2) pairs, every
+// thread keeps P Fourier points of all k+1 output polynomials in registers, the Fourier key is
+// read straight from L2 with 16-byte coalesced loads in the very order the registers need it,
+// and mod-switch / rotation / gadget decomposition / FFT / product / inverse FFT / torus rounding
+// / sample extraction never leave the SM.
+#include "common.cuh"
+#include "fft.cuh"
+#include "../../include/concrete_b200.h"
+#include <cmath>
+#include <map>
+#include <mutex>
+#include <vector>
+
+namespace {
+
+// ------------------------------------------------------------------------------------------
+// Twiddle tables: tw[2^s + b] = exp(i*pi*(1 + 4*bitrev_s(b)) / 2^(s+2)), one per (device, LOGM)
+// ------------------------------------------------------------------------------------------
+std::mutex g_tw_mutex;
+std::map<std::pair<int, int>, double2 *> g_tw_cache;
+
+u32 bitrev(u32 x, int bits) {
+  u32 r = 0;
+  for (int i = 0; i < bits; ++i) r = (r << 1) | ((x >> i) & 1);
+  return r;
+}
+
+const double2 *get_twiddles(int gpu, int logm) {
+  std::lock_guard<std::mutex> g(g_tw_mutex);
+  auto key = std::make_pair(gpu, logm);
+  auto it = g_tw_cache.find(key);
+  if (it != g_tw_cache.end()) return it->second;
+  const size_t M = (size_t)1 << logm;
+  std::vector<double2> h(M);
+  h[0] = make_double2(1.0, 0.0);
+  const long double pi = 3.14159265358979323846264338327950288L;
+  for (int s = 0; s < logm; ++s)
+    for (u32 b = 0; b < (1u << s); ++b) {
+      long double ang = pi * (long double)(1 + 4 * (uint64_t)bitrev(b, s)) /
+                        (long double)((uint64_t)1 << (s + 2));
+      h[((size_t)1 << s) + b] = make_double2((double)cosl(ang), (double)sinl(ang));
+    }
+  double2 *d = nullptr;
+  CB_CHECK(cudaMalloc(&d, M * sizeof(double2)));
+  CB_CHECK(cudaMemcpy(d, h.data(), M * sizeof(double2), cudaMemcpyHostToDevice));
+  g_tw_cache[key] = d;
+  return d;
+}
+
+// ------------------------------------------------------------------------------------------
+// Integer helpers (restate decomposer.rs:23-47, iter.rs:121-133, fft_impl/common.rs:17-25,
+// commons/math/torus/mod.rs:72-78)
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ u64 closest_representable(u64 x, u32 shift_m1) {
+  u64 r = x >> shift_m1;
+  r += 1;
+  r &= ~(u64)1;
+  return r << shift_m1;
+}
+__device__ __forceinline__ u64 decompose_one_level(u64 &state, u64 mask, u32 base_log) {
+  u64 res = state & mask;
+  state >>= base_log;
+  u64 carry = ((res - 1) | state) & res;
+  carry >>= (base_log - 1);
+  state += carry;
+  return res - (carry << base_log);
+}
+__device__ __forceinline__ u32 modulus_switch(u64 x, u32 log_modulus) {
+  return (u32)((x + ((u64)1 << (63 - log_modulus))) >> (64 - log_modulus));
+}
+__device__ __forceinline__ u64 from_torus(double x) {
+  double fr = x - rint(x);
+  return (u64)__double2ll_rn(fr * 18446744073709551616.0);
+}
+
+// ------------------------------------------------------------------------------------------
+// Kernel configuration per (K, LOGN)
+// ------------------------------------------------------------------------------------------
+template <int K, int LOGN> struct PbsCfg {
+  static constexpr int LOGM = LOGN - 1;
+  // points per thread: keep (K+1)*P*2 doubles of Fourier accumulators in registers
+  static constexpr int LOGP_WANT = (K <= 2) ? 3 : (K <= 5 ? 2 : 1);
+  static constexpr int LOGP_MIN = (LOGM - LOGP_WANT > 10) ? (LOGM - 10) : LOGP_WANT; // T <= 1024
+  static constexpr int LOGP = (LOGM - LOGP_MIN < 5) ? (LOGM - 5) : LOGP_MIN;         // T >= 32
+  using F = cbfft::Cfg<LOGM, LOGP>;
+  static constexpr int T = F::T;
+  static constexpr int M = F::M;
+  static constexpr int N = 2 * M;
+  static constexpr int P = F::P;
+  static constexpr int REGS = (K == 1) ? 128 : ((K == 2) ? 168 : 128);
+  static constexpr int MINB_R = (65536 / REGS) / T;
+  static constexpr int MINB = MINB_R < 1 ? 1 : (MINB_R > 16 ? 16 : MINB_R);
+  static constexpr size_t FBUF_BYTES = (size_t)F::BUF_ELEMS * sizeof(double2);
+  static constexpr size_t ACC_BYTES = (size_t)(K + 1) * N * sizeof(u64);
+  // accumulator in shared memory if it fits in the 227 KB opt-in limit (with ~4 KB for a_hat)
+  static constexpr bool ACC_GLOBAL = (FBUF_BYTES + ACC_BYTES + 4096) > 232448;
+};
+
+struct PbsArgs {
+  u64 *lwe_out;
+  const u64 *out_idx;
+  const u64 *lut_vector;
+  const u64 *lut_idx;
+  const u64 *lwe_in;
+  const u64 *in_idx;
+  const double2 *bsk;
+  const double2 *tw;
+  ulonglong2 *global_acc; // [gridDim.x][(K+1)*M] pairs, only when ACC_GLOBAL
+  u32 n, base_log, level, num_samples, lut_count, lut_stride;
+};
+
+template <int K, int LOGN>
+__global__ void __launch_bounds__(PbsCfg<K, LOGN>::T, PbsCfg<K, LOGN>::MINB)
+pbs_kernel(const PbsArgs a) {
+  using C = PbsCfg<K, LOGN>;
+  constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
+  constexpr int GS = K + 1;
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *fbuf = reinterpret_cast<double2 *>(smem);
+  ulonglong2 *acc;
+  unsigned short *s_ahat;
+  if (C::ACC_GLOBAL) {
+    acc = a.global_acc + (size_t)blockIdx.x * GS * M;
+    s_ahat = reinterpret_cast<unsigned short *>(smem + C::FBUF_BYTES);
+  } else {
+    acc = reinterpret_cast<ulonglong2 *>(smem + C::FBUF_BYTES);
+    s_ahat = reinterpret_cast<unsigned short *>(smem + C::FBUF_BYTES + C::ACC_BYTES);
+  }
+  const int t = threadIdx.x;
+  const u32 n = a.n, base_log = a.base_log, level = a.level;
+  const u64 mask = ((u64)1 << base_log) - 1;
+  const u32 round_shift = 64 - base_log * level - 1; // closest_representable shift
+  const u32 state_shift = 64 - base_log * level;
+  const double2 *__restrict__ tw = a.tw;
+  const size_t out_size = (size_t)K * N + 1;
+
+  for (u32 sample = blockIdx.x; sample < a.num_samples; sample += gridDim.x) {
+    const u64 *lwe = a.lwe_in + a.in_idx[sample] * (u64)(n + 1);
+    for (u32 i = t; i < n; i += T) s_ahat[i] = (unsigned short)modulus_switch(lwe[i], LOGN + 1);
+    const u32 b_hat = modulus_switch(lwe[n], LOGN + 1);
+
+    // ACC <- LUT * X^(-b_hat)   (polynomial_algorithms.rs:500-539)
+    const u64 *lut = a.lut_vector + a.lut_idx[sample] * (u64)(GS * N);
+#pragma unroll
+    for (int c = 0; c < GS; ++c) {
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        ulonglong2 v;
+        {
+          const u32 u = (j + b_hat) & (2 * N - 1);
+          const u64 w = lut[c * N + (u & (N - 1))];
+          v.x = (u < (u32)N) ? w : (u64)0 - w;
+        }
+        {
+          const u32 u = (j + M + b_hat) & (2 * N - 1);
+          const u64 w = lut[c * N + (u & (N - 1))];
+          v.y = (u < (u32)N) ? w : (u64)0 - w;
+        }
+        acc[c * M + j] = v;
+      }
+    }
+    __syncthreads();
+
+    for (u32 i = 0; i < n; ++i) {
+      const u32 a_hat = s_ahat[i];
+      if (a_hat == 0) continue; // X^0 - 1 = 0: the CMUX adds nothing (bootstrap.rs:287)
+
+      double2 oacc[GS][P];
+#pragma unroll
+      for (int c = 0; c < GS; ++c)
+#pragma unroll
+        for (int p = 0; p < P; ++p) oacc[c][p] = make_double2(0.0, 0.0);
+
+#pragma unroll 1
+      for (int r = 0; r < GS; ++r) {
+        // ct1_r = ACC_r * X^a_hat - ACC_r  (polynomial_algorithms.rs:610-690), then
+        // closest_representable and the decomposition state (fft64/math/decomposition.rs:27-46)
+        u64 st_re[P], st_im[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+          const int j = t + p * T;
+          const u32 s = (u32)(j - (int)a_hat) & (2 * N - 1);
+          const u32 q = s >> LOGM;
+          const ulonglong2 src = acc[r * M + (s & (M - 1))];
+          const ulonglong2 own = acc[r * M + j];
+          const u64 ra = (q & 1) ? src.y : src.x;
+          const u64 rb = (q & 1) ? src.x : src.y;
+          // (-i)^q * (A + iB): q=0 (A,B) q=1 (B,-A) q=2 (-A,-B) q=3 (-B,A)
+          const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
+          const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
+          st_re[p] = closest_representable(rot_re - own.x, round_shift) >> state_shift;
+          st_im[p] = closest_representable(rot_im - own.y, round_shift) >> state_shift;
+        }
+#pragma unroll 1
+        for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
+          double2 x[P];
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            x[p].x = __int2double_rn((int)(u32)decompose_one_level(st_re[p], mask, base_log));
+            x[p].y = __int2double_rn((int)(u32)decompose_one_level(st_im[p], mask, base_log));
+          }
+          cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw);
+          const double2 *__restrict__ g =
+              a.bsk + ((((size_t)i * level + m) * GS + r) * GS) * M + t;
+#pragma unroll
+          for (int c = 0; c < GS; ++c) {
+#pragma unroll
+            for (int p = 0; p < P; ++p) {
+              const double2 w = __ldg(&g[(size_t)c * M + p * T]);
+              oacc[c][p].x = fma(x[p].x, w.x, fma(-x[p].y, w.y, oacc[c][p].x));
+              oacc[c][p].y = fma(x[p].x, w.y, fma(x[p].y, w.x, oacc[c][p].y));
+            }
+          }
+        }
+      }
+      if (C::F::NPASS == 1) __syncthreads(); // all rotated reads done before ACC changes
+#pragma unroll
+      for (int c = 0; c < GS; ++c) {
+        cbfft::inverse<LOGM, LOGP>(oacc[c], fbuf, t, tw);
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+          const int j = t + p * T;
+          ulonglong2 v = acc[c * M + j];
+          v.x += from_torus(oacc[c][p].x);
+          v.y += from_torus(oacc[c][p].y);
+          acc[c * M + j] = v;
+        }
+      }
+      __syncthreads();
+    }
+
+    // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride
+    for (u32 li = 0; li < a.lut_count; ++li) {
+      const u32 nth = li * a.lut_stride;
+      u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
+      for (int x = t; x < K * N; x += T) {
+        const int c = x >> LOGN, j = x & (N - 1);
+        const int src = (j <= (int)nth) ? ((int)nth - j) : (N + (int)nth - j);
+        const ulonglong2 pr = acc[c * M + (src & (M - 1))];
+        const u64 v = (src < M) ? pr.x : pr.y;
+        out[x] = (j <= (int)nth) ? v : (u64)0 - v;
+      }
+      if (t == 0) {
+        const ulonglong2 pr = acc[K * M + (nth & (M - 1))];
+        out[(size_t)K * N] = (nth < (u32)M) ? pr.x : pr.y;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4: standard-domain BSK -> Fourier, in place, one CTA per polynomial.
+// Output polynomial `poly` occupies the same N*8 bytes as the input polynomial `poly`:
+//   dst[p*T + t] = F_{q = t*P + p} / M      (1/M = the inverse transform's normalisation)
+// ------------------------------------------------------------------------------------------
+template <int K, int LOGN>
+__global__ void __launch_bounds__(PbsCfg<K, LOGN>::T)
+bsk_convert_kernel(double2 *bsk, const double2 *__restrict__ tw, size_t num_polys) {
+  using C = PbsCfg<K, LOGN>;
+  constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, P = C::P, T = C::T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *fbuf = reinterpret_cast<double2 *>(smem);
+  const int t = threadIdx.x;
+  for (size_t poly = blockIdx.x; poly < num_polys; poly += gridDim.x) {
+    const u64 *src = reinterpret_cast<const u64 *>(bsk + poly * M);
+    double2 x[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const int j = t + p * T;
+      // convert_forward_torus (fft/mod.rs:201-222): signed value * 2^-64
+      x[p].x = __ll2double_rn((i64)src[j]) * 5.421010862427522170037e-20;
+      x[p].y = __ll2double_rn((i64)src[j + M]) * 5.421010862427522170037e-20;
+    }
+    __syncthreads(); // every read of this polynomial precedes the in-place writes
+    cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw);
+    double2 *dst = bsk + poly * M;
+    const double inv_m = 1.0 / (double)M;
+#pragma unroll
+    for (int p = 0; p < P; ++p) dst[p * T + t] = make_double2(x[p].x * inv_m, x[p].y * inv_m);
+    __syncthreads();
+  }
+}
+
+// FFT test hook: out = in1 (*) in2 negacyclic, doubles.
+template <int K, int LOGN>
+__global__ void __launch_bounds__(PbsCfg<K, LOGN>::T)
+poly_mul_kernel(const double *in1, const double *in2, double *out,
+                const double2 *__restrict__ tw, u32 total) {
+  using C = PbsCfg<K, LOGN>;
+  constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *fbuf = reinterpret_cast<double2 *>(smem);
+  const int t = threadIdx.x;
+  for (u32 poly = blockIdx.x; poly < total; poly += gridDim.x) {
+    double2 x[P], y[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const int j = t + p * T;
+      x[p] = make_double2(in1[(size_t)poly * N + j], in1[(size_t)poly * N + j + M]);
+      y[p] = make_double2(in2[(size_t)poly * N + j], in2[(size_t)poly * N + j + M]);
+    }
+    cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw);
+    cbfft::forward<LOGM, LOGP>(y, fbuf, t, tw);
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const double2 u = x[p], v = y[p];
+      x[p] = make_double2(u.x * v.x - u.y * v.y, u.x * v.y + u.y * v.x);
+    }
+    cbfft::inverse<LOGM, LOGP>(x, fbuf, t, tw);
+    const double inv_m = 1.0 / (double)M;
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const int j = t + p * T;
+      out[(size_t)poly * N + j] = x[p].x * inv_m;
+      out[(size_t)poly * N + j + M] = x[p].y * inv_m;
+    }
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Host-side dispatch
+// ------------------------------------------------------------------------------------------
+struct Variant {
+  void (*pbs)(const PbsArgs);
+  void (*convert)(double2 *, const double2 *, size_t);
+  void (*polymul)(const double *, const double *, double *, const double2 *, u32);
+  int T;
+  size_t fbuf_bytes, acc_bytes;
+  bool acc_global;
+};
+
+template <int K, int LOGN> Variant make_variant() {
+  using C = PbsCfg<K, LOGN>;
+  Variant v;
+  v.pbs = pbs_kernel<K, LOGN>;
+  v.convert = bsk_convert_kernel<K, LOGN>;
+  v.polymul = poly_mul_kernel<K, LOGN>;
+  v.T = C::T;
+  v.fbuf_bytes = C::FBUF_BYTES;
+  v.acc_bytes = C::ACC_BYTES;
+  v.acc_global = C::ACC_GLOBAL;
+  return v;
+}
+
+bool get_variant(u32 k, u32 N, Variant &v) {
+  int logn = 0;
+  while ((1u << logn) < N) ++logn;
+  if ((1u << logn) != N) return false;
+#define CB_CASE(KK, LL)                                                                  \
+  if (k == KK && logn == LL) {                                                           \
+    v = make_variant<KK, LL>();                                                          \
+    return true;                                                                         \
+  }
+  CB_CASE(1, 8) CB_CASE(1, 9) CB_CASE(1, 10) CB_CASE(1, 11) CB_CASE(1, 12) CB_CASE(1, 13)
+  CB_CASE(1, 14)
+  CB_CASE(2, 8) CB_CASE(2, 9) CB_CASE(2, 10) CB_CASE(2, 11) CB_CASE(2, 12)
+  CB_CASE(3, 8) CB_CASE(3, 9) CB_CASE(3, 10) CB_CASE(3, 11)
+  CB_CASE(4, 8) CB_CASE(4, 9)
+  CB_CASE(5, 8) CB_CASE(5, 9)
+  CB_CASE(6, 8)
+#undef CB_CASE
+  return false;
+}
+
+constexpr u32 PBS_MAGIC = 0xB200CB01u;
+
+struct PbsBuffer {
+  u32 magic;
+  int gpu;
+  u32 k, N, level, max_samples;
+  int grid_cap;           // resident CTAs for the persistent launch
+  size_t smem_fixed;      // dynamic smem without the a_hat table
+  ulonglong2 *global_acc; // device scratch when the accumulator does not fit in smem
+  Variant v;
+};
+
+size_t pbs_smem_bytes(const Variant &v, u32 n) {
+  size_t ahat = (((size_t)n * 2 + 15) / 16) * 16;
+  return v.fbuf_bytes + (v.acc_global ? 0 : v.acc_bytes) + ahat;
+}
+
+} // namespace
+
+// internal entry points shared with legacy.cu / chain
+void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N, u32 level,
+                    u32 count, bool allocate) {
+  Variant v;
+  if (!get_variant(k, N, v))
+    CB_PANIC("Cuda error (classical PBS): unsupported (glwe_dimension=%u, polynomial_size=%u). "
+             "Supported N: powers of two in [256..16384].",
+             k, N);
+  PbsBuffer *b = new PbsBuffer();
+  b->magic = PBS_MAGIC;
+  b->gpu = gpu;
+  b->k = k;
+  b->N = N;
+  b->level = level;
+  b->max_samples = count;
+  b->v = v;
+  b->global_acc = nullptr;
+  get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
+  // size the persistent grid from the real occupancy with a typical a_hat table (n <= 2048)
+  const size_t smem = pbs_smem_bytes(v, 2048);
+  CB_CHECK(cudaFuncSetAttribute(v.pbs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0, sms = 0;
+  CB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, v.pbs, v.T, smem));
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  if (per_sm < 1)
+    CB_PANIC("Cuda error (classical PBS): kernel does not fit on an SM (smem %zu B)", smem);
+  b->grid_cap = per_sm * sms;
+  if (v.acc_global && allocate) {
+    size_t ctas = (size_t)std::min<u32>((u32)b->grid_cap, count ? count : 1);
+    CB_CHECK(cudaMallocAsync((void **)&b->global_acc, ctas * v.acc_bytes, stream));
+  }
+  *buffer = reinterpret_cast<int8_t *>(b);
+}
+
+void cb_pbs_cleanup(cudaStream_t stream, int gpu, int8_t **buffer) {
+  (void)gpu;
+  if (!buffer || !*buffer) return;
+  PbsBuffer *b = reinterpret_cast<PbsBuffer *>(*buffer);
+  if (b->magic != PBS_MAGIC) CB_PANIC("Cuda error (classical PBS): invalid pbs buffer");
+  if (b->global_acc) CB_CHECK(cudaFreeAsync(b->global_acc, stream));
+  b->magic = 0;
+  delete b; // the reference leaks the host object (programmable_bootstrap.cu cleanup); we do not
+  *buffer = nullptr;
+}
+
+void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_idx,
+                   const u64 *lut_vector, const u64 *lut_idx, const u64 *lwe_in,
+                   const u64 *in_idx, const double2 *bsk, int8_t *buffer, u32 n, u32 k, u32 N,
+                   u32 base_log, u32 level, u32 num_samples, u32 lut_count, u32 lut_stride) {
+  if (num_samples == 0) return;
+  PbsBuffer *b = reinterpret_cast<PbsBuffer *>(buffer);
+  if (!b || b->magic != PBS_MAGIC) CB_PANIC("Cuda error (classical PBS): invalid pbs buffer");
+  if (b->k != k || b->N != N)
+    CB_PANIC("Cuda error (classical PBS): buffer was created for (k=%u,N=%u), called with "
+             "(k=%u,N=%u)", b->k, b->N, k, N);
+  if (base_log == 0 || level == 0 || base_log * level >= 64 || base_log > 31)
+    CB_PANIC("Cuda error (classical PBS): unsupported decomposition base_log=%u level=%u",
+             base_log, level);
+  if (lut_count == 0) lut_count = 1;
+  if ((u64)(lut_count - 1) * lut_stride >= N)
+    CB_PANIC("Cuda error (classical PBS): lut_count*lut_stride exceeds polynomial size");
+  const Variant &v = b->v;
+  u32 grid = std::min<u32>((u32)b->grid_cap, num_samples);
+  if (v.acc_global) {
+    if (!b->global_acc)
+      CB_PANIC("Cuda error (classical PBS): scratch was created without GPU memory");
+    grid = std::min<u32>(grid, std::max<u32>(1, std::min<u32>((u32)b->grid_cap, b->max_samples)));
+  }
+  PbsArgs a;
+  a.lwe_out = lwe_out;
+  a.out_idx = out_idx;
+  a.lut_vector = lut_vector;
+  a.lut_idx = lut_idx;
+  a.lwe_in = lwe_in;
+  a.in_idx = in_idx;
+  a.bsk = bsk;
+  a.tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
+  a.global_acc = b->global_acc;
+  a.n = n;
+  a.base_log = base_log;
+  a.level = level;
+  a.num_samples = num_samples;
+  a.lut_count = lut_count;
+  a.lut_stride = lut_stride;
+  const size_t smem = pbs_smem_bytes(v, n);
+  CB_CHECK(cudaFuncSetAttribute(v.pbs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  v.pbs<<<grid, v.T, smem, stream>>>(a);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_host, u32 n, u32 k,
+                    u32 level, u32 N, bool src_on_device) {
+  Variant v;
+  if (!get_variant(k, N, v))
+    CB_PANIC("Cuda error (convert BSK): unsupported (glwe_dimension=%u, polynomial_size=%u)", k,
+             N);
+  const size_t polys = (size_t)n * level * (k + 1) * (k + 1);
+  const size_t bytes = polys * N * sizeof(u64);
+  if (bytes == 0) return;
+  CB_CHECK(cudaMemcpyAsync(dest, src_host, bytes,
+                           src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                           stream));
+  const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
+  CB_CHECK(cudaFuncSetAttribute(v.convert, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.fbuf_bytes));
+  int sms = 0;
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  const u32 grid = (u32)std::min<size_t>(polys, (size_t)sms * 8);
+  v.convert<<<grid, v.T, v.fbuf_bytes, stream>>>(reinterpret_cast<double2 *>(dest), tw, polys);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+extern "C" {
+
+void cuda_convert_lwe_programmable_bootstrap_key_64(void *stream, uint32_t gpu_index, void *dest,
+                                                    void *src, uint32_t input_lwe_dim,
+                                                    uint32_t glwe_dim, uint32_t level_count,
+                                                    uint32_t polynomial_size) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cudaPointerAttributes attr;
+  bool on_device = false;
+  if (cudaPointerGetAttributes(&attr, src) == cudaSuccess)
+    on_device = (attr.type == cudaMemoryTypeDevice);
+  else
+    (void)cudaGetLastError();
+  cb_bsk_convert(as_stream(stream), gpu_index, dest, src, input_lwe_dim, glwe_dim, level_count,
+                 polynomial_size, on_device);
+}
+
+void scratch_cuda_programmable_bootstrap_64(void *stream, uint32_t gpu_index, int8_t **buffer,
+                                            uint32_t glwe_dimension, uint32_t polynomial_size,
+                                            uint32_t level_count,
+                                            uint32_t input_lwe_ciphertext_count,
+                                            bool allocate_gpu_memory) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_scratch(as_stream(stream), gpu_index, buffer, glwe_dimension, polynomial_size,
+                 level_count, input_lwe_ciphertext_count, allocate_gpu_memory);
+}
+
+void cuda_programmable_bootstrap_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, void *lwe_output_indexes,
+    void *lut_vector, void *lut_vector_indexes, void *lwe_array_in, void *lwe_input_indexes,
+    void *bootstrapping_key, int8_t *buffer, uint32_t lwe_dimension, uint32_t glwe_dimension,
+    uint32_t polynomial_size, uint32_t base_log, uint32_t level_count, uint32_t num_samples,
+    uint32_t lut_count, uint32_t lut_stride) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_launch(as_stream(stream), gpu_index, (u64 *)lwe_array_out,
+                (const u64 *)lwe_output_indexes, (const u64 *)lut_vector,
+                (const u64 *)lut_vector_indexes, (const u64 *)lwe_array_in,
+                (const u64 *)lwe_input_indexes, (const double2 *)bootstrapping_key, buffer,
+                lwe_dimension, glwe_dimension, polynomial_size, base_log, level_count,
+                num_samples, lut_count, lut_stride);
+}
+
+void cleanup_cuda_programmable_bootstrap(void *stream, uint32_t gpu_index, int8_t **pbs_buffer) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_cleanup(as_stream(stream), gpu_index, pbs_buffer);
+}
+
+// "amortized" names: same fused kernel (one CTA per ciphertext is exactly the amortized design,
+// programmable_bootstrap_amortized.cuh:48-213, without its 48 KiB shared-memory ceiling).
+void scratch_cuda_programmable_bootstrap_amortized_64(void *stream, uint32_t gpu_index,
+                                                      int8_t **pbs_buffer,
+                                                      uint32_t glwe_dimension,
+                                                      uint32_t polynomial_size,
+                                                      uint32_t input_lwe_ciphertext_count,
+                                                      bool allocate_gpu_memory) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_scratch(as_stream(stream), gpu_index, pbs_buffer, glwe_dimension, polynomial_size, 0,
+                 input_lwe_ciphertext_count, allocate_gpu_memory);
+}
+
+void cuda_programmable_bootstrap_amortized_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, void *lwe_output_indexes,
+    void *lut_vector, void *lut_vector_indexes, void *lwe_array_in, void *lwe_input_indexes,
+    void *bootstrapping_key, int8_t *pbs_buffer, uint32_t lwe_dimension,
+    uint32_t glwe_dimension, uint32_t polynomial_size, uint32_t base_log, uint32_t level_count,
+    uint32_t num_samples) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_launch(as_stream(stream), gpu_index, (u64 *)lwe_array_out,
+                (const u64 *)lwe_output_indexes, (const u64 *)lut_vector,
+                (const u64 *)lut_vector_indexes, (const u64 *)lwe_array_in,
+                (const u64 *)lwe_input_indexes, (const double2 *)bootstrapping_key, pbs_buffer,
+                lwe_dimension, glwe_dimension, polynomial_size, base_log, level_count,
+                num_samples, 1, 1);
+}
+
+void cleanup_cuda_programmable_bootstrap_amortized(void *stream, uint32_t gpu_index,
+                                                   int8_t **pbs_buffer) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  cb_pbs_cleanup(as_stream(stream), gpu_index, pbs_buffer);
+}
+
+void cuda_fourier_polynomial_mul(void *stream, uint32_t gpu_index, void *input1, void *input2,
+                                 void *output, uint32_t polynomial_size,
+                                 uint32_t total_polynomials) {
+  CB_CHECK(cudaSetDevice(gpu_index));
+  if (total_polynomials == 0) return;
+  Variant v;
+  if (!get_variant(1, polynomial_size, v))
+    CB_PANIC("Cuda error (fourier mul): unsupported polynomial size %u", polynomial_size);
+  const double2 *tw =
+      get_twiddles(gpu_index, (int)std::lround(std::log2((double)polynomial_size)) - 1);
+  CB_CHECK(cudaFuncSetAttribute(v.polymul, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.fbuf_bytes));
+  const u32 grid = std::min<u32>(total_polynomials, 148 * 8);
+  v.polymul<<<grid, v.T, v.fbuf_bytes, as_stream(stream)>>>(
+      (const double *)input1, (const double *)input2, (double *)output, tw, total_polynomials);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+} // extern "C"

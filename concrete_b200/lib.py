@@ -1,0 +1,84 @@
+"""ctypes declaration of every symbol in include/concrete_b200.h (the C-ABI boundary)."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+vp, u32, u64, i8pp = C.c_void_p, C.c_uint32, C.c_uint64, C.POINTER(C.POINTER(C.c_int8))
+i8p = C.POINTER(C.c_int8)
+
+# name -> (restype, argtypes); mirrors include/concrete_b200.h one to one
+SIGNATURES = {
+    "cuda_create_stream": (vp, [u32]),
+    "cuda_destroy_stream": (None, [vp, u32]),
+    "cuda_synchronize_stream": (None, [vp, u32]),
+    "cuda_malloc": (vp, [u64, u32]),
+    "cuda_malloc_async": (vp, [u64, vp, u32]),
+    "cuda_check_valid_malloc": (None, [u64, u32]),
+    "cuda_memcpy_async_to_gpu": (None, [vp, vp, u64, vp, u32]),
+    "cuda_memcpy_async_gpu_to_gpu": (None, [vp, vp, u64, vp, u32]),
+    "cuda_memcpy_gpu_to_gpu": (None, [vp, vp, u64, u32]),
+    "cuda_memcpy_async_to_cpu": (None, [vp, vp, u64, vp, u32]),
+    "cuda_memset_async": (None, [vp, u64, u64, vp, u32]),
+    "cuda_get_number_of_gpus": (C.c_int, []),
+    "cuda_synchronize_device": (None, [u32]),
+    "cuda_drop": (None, [vp, u32]),
+    "cuda_drop_async": (None, [vp, vp, u32]),
+    "cuda_get_max_shared_memory": (C.c_int, [u32]),
+    "cuda_keyswitch_lwe_ciphertext_vector_64": (None, [vp, u32, vp, vp, vp, vp, vp, u32, u32, u32, u32, u32]),
+    "cuda_convert_lwe_programmable_bootstrap_key_64": (None, [vp, u32, vp, vp, u32, u32, u32, u32]),
+    "scratch_cuda_programmable_bootstrap_64": (None, [vp, u32, i8pp, u32, u32, u32, u32, C.c_bool]),
+    "cuda_programmable_bootstrap_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, vp, vp, i8p, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "cleanup_cuda_programmable_bootstrap": (None, [vp, u32, i8pp]),
+    "scratch_cuda_programmable_bootstrap_amortized_64": (None, [vp, u32, i8pp, u32, u32, u32, C.c_bool]),
+    "cuda_programmable_bootstrap_amortized_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, vp, vp, i8p, u32, u32, u32, u32, u32, u32]),
+    "cleanup_cuda_programmable_bootstrap_amortized": (None, [vp, u32, i8pp]),
+    "cuda_fourier_polynomial_mul": (None, [vp, u32, vp, vp, vp, u32, u32]),
+    "cuda_negate_lwe_ciphertext_vector_64": (None, [vp, u32, vp, vp, u32, u32]),
+    "cuda_add_lwe_ciphertext_vector_64": (None, [vp, u32, vp, vp, vp, u32, u32]),
+    "cuda_add_lwe_ciphertext_vector_plaintext_vector_64": (None, [vp, u32, vp, vp, vp, u32, u32]),
+    "cuda_mult_lwe_ciphertext_vector_cleartext_vector_64": (None, [vp, u32, vp, vp, vp, u32, u32]),
+    "cuda_convert_lwe_bootstrap_key_64": (None, [vp, vp, vp, u32, u32, u32, u32, u32]),
+    "scratch_cuda_bootstrap_low_latency_64": (None, [vp, u32, i8pp, u32, u32, u32, u32, u32, C.c_bool]),
+    "cuda_bootstrap_low_latency_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, i8p, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "cleanup_cuda_bootstrap_low_latency": (None, [vp, u32, i8pp]),
+    "scratch_cuda_bootstrap_amortized_64": (None, [vp, u32, i8pp, u32, u32, u32, u32, C.c_bool]),
+    "cuda_bootstrap_amortized_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, i8p, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "cleanup_cuda_bootstrap_amortized": (None, [vp, u32, i8pp]),
+    "cuda_keyswitch_lwe_ciphertext_vector_64_legacy": (None, [vp, u32, vp, vp, vp, u32, u32, u32, u32, u32]),
+    "cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, vp, i8p, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "concrete_b200_version": (C.c_char_p, []),
+    "concrete_b200_kernel_launches": (u64, []),
+}
+
+
+def library_path() -> str:
+    return os.path.join(_HERE, "libconcrete_b200.so")
+
+
+def load_library():
+    """Load libconcrete_b200.so.  No fallback: a missing library is an error."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = library_path()
+    if not os.path.exists(path):
+        raise RuntimeError(
+            f"{path} is missing: build it with `python -m concrete_b200.build` "
+            "(nvcc, sm_100a).  concrete_b200 has no CPU fallback."
+        )
+    lib = C.CDLL(path, mode=C.RTLD_LOCAL)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+        fn.restype = res
+        fn.argtypes = args
+    _LIB = lib
+    return lib

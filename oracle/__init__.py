@@ -1,0 +1,233 @@
+"""ctypes binding of the CPU oracle (oracle/tfhe_oracle.cpp).
+
+TEST INFRASTRUCTURE ONLY: importable from tests/, __graft_entry__.smoke() and
+bench.py's cpu_baseline / ``--impl reference`` legs.  The product package
+``concrete_b200`` never imports this module.
+
+Every function mirrors one C entry point; see the C++ header comment for the
+reference file:line each one restates.  Arrays are numpy ``uint64`` (ciphertexts,
+keys) or ``complex128`` (Fourier keys), C-contiguous.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+u64p = C.POINTER(C.c_uint64)
+
+
+def build(native: bool = False) -> str:
+    """Compile the oracle with the committed Makefile; returns the .so path."""
+    target = "liboracle_native.so" if native else "liboracle.so"
+    subprocess.run(["make", "-C", _HERE, target], check=True, capture_output=True)
+    return os.path.join(_HERE, target)
+
+
+def lib(native: bool = False):
+    global _LIB
+    if _LIB is not None and not native:
+        return _LIB
+    path = os.path.join(_HERE, "liboracle_native.so" if native else "liboracle.so")
+    src = os.path.join(_HERE, "tfhe_oracle.cpp")
+    if not os.path.exists(path) or (
+        os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(path)
+    ):
+        build(native)
+    l = C.CDLL(path)
+    l.orc_closest_representable_u8.restype = C.c_uint8
+    l.orc_closest_representable_u8.argtypes = [C.c_uint8, C.c_uint, C.c_uint]
+    l.orc_closest_representable_u32.restype = C.c_uint32
+    l.orc_closest_representable_u32.argtypes = [C.c_uint32, C.c_uint, C.c_uint]
+    l.orc_closest_representable_u64.restype = C.c_uint64
+    l.orc_closest_representable_u64.argtypes = [C.c_uint64, C.c_uint, C.c_uint]
+    l.orc_decompose_u32.argtypes = [C.c_uint32, C.c_uint, C.c_uint, C.POINTER(C.c_uint32)]
+    l.orc_decompose_u64.argtypes = [C.c_uint64, C.c_uint, C.c_uint, u64p]
+    l.orc_modulus_switch.restype = C.c_uint64
+    l.orc_modulus_switch.argtypes = [C.c_uint64, C.c_uint]
+    l.orc_from_torus.restype = C.c_uint64
+    l.orc_from_torus.argtypes = [C.c_double]
+    l.orc_num_threads.restype = C.c_int
+    l.orc_set_num_threads.argtypes = [C.c_int]
+    if not native:
+        _LIB = l
+    return l
+
+
+def _p(a: np.ndarray, dtype=np.uint64):
+    assert a.dtype == dtype and a.flags["C_CONTIGUOUS"], (a.dtype, a.flags)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def num_threads(native=False) -> int:
+    return lib(native).orc_num_threads()
+
+
+# ---------------------------------------------------------------- scalar pieces
+def closest_representable(x: int, level: int, base_log: int, bits: int = 64) -> int:
+    f = getattr(lib(), f"orc_closest_representable_u{bits}")
+    return int(f(x, level, base_log))
+
+
+def decompose(x: int, level: int, base_log: int, bits: int = 64):
+    """Signed digits, index 0 = level `level` (least significant) ... last = level 1."""
+    if bits == 64:
+        out = (C.c_uint64 * level)()
+        lib().orc_decompose_u64(x, level, base_log, out)
+        return [v - (1 << 64) if v >> 63 else v for v in out]
+    out = (C.c_uint32 * level)()
+    lib().orc_decompose_u32(x, level, base_log, out)
+    return [v - (1 << 32) if v >> 31 else v for v in out]
+
+
+def modulus_switch(x: int, log_modulus: int) -> int:
+    return int(lib().orc_modulus_switch(x, log_modulus))
+
+
+def from_torus(x: float) -> int:
+    return int(lib().orc_from_torus(x))
+
+
+def monomial_div(poly: np.ndarray, degree: int) -> np.ndarray:
+    out = np.empty_like(poly)
+    if poly.dtype == np.uint8:
+        lib().orc_monomial_div_u8(_p(out, np.uint8), _p(poly, np.uint8), C.c_size_t(len(poly)), C.c_size_t(degree))
+    else:
+        lib().orc_monomial_div_u64(_p(out), _p(poly), C.c_size_t(len(poly)), C.c_size_t(degree))
+    return out
+
+
+def monomial_mul(poly: np.ndarray, degree: int) -> np.ndarray:
+    out = np.empty_like(poly)
+    if poly.dtype == np.uint8:
+        lib().orc_monomial_mul_u8(_p(out, np.uint8), _p(poly, np.uint8), C.c_size_t(len(poly)), C.c_size_t(degree))
+    else:
+        lib().orc_monomial_mul_u64(_p(out), _p(poly), C.c_size_t(len(poly)), C.c_size_t(degree))
+    return out
+
+
+def monomial_mul_and_subtract(poly: np.ndarray, degree: int) -> np.ndarray:
+    out = np.empty_like(poly)
+    lib().orc_monomial_mul_and_subtract_u64(_p(out), _p(poly), C.c_size_t(len(poly)), C.c_size_t(degree))
+    return out
+
+
+def sample_extract(glwe: np.ndarray, k: int, N: int, nth: int = 0) -> np.ndarray:
+    out = np.empty(k * N + 1, dtype=np.uint64)
+    lib().orc_sample_extract_u64(_p(out), _p(glwe), C.c_size_t(k), C.c_size_t(N), C.c_size_t(nth))
+    return out
+
+
+def negacyclic_mul_schoolbook(a, b):
+    out = np.empty_like(a)
+    lib().orc_negacyclic_mul_schoolbook(_p(out), _p(a), _p(b), C.c_size_t(len(a)))
+    return out
+
+
+def negacyclic_mul_binary(a, s):
+    out = np.empty_like(a)
+    lib().orc_negacyclic_mul_binary(_p(out), _p(a), _p(s), C.c_size_t(len(a)))
+    return out
+
+
+# ---------------------------------------------------------------- FFT pieces
+def fft_forward_as_torus(poly: np.ndarray) -> np.ndarray:
+    N = len(poly)
+    out = np.empty(N // 2, dtype=np.complex128)
+    lib().orc_fft_forward_as_torus(_p(out, np.complex128), _p(poly), C.c_size_t(N))
+    return out
+
+
+def fft_forward_as_integer(poly: np.ndarray) -> np.ndarray:
+    N = len(poly)
+    out = np.empty(N // 2, dtype=np.complex128)
+    lib().orc_fft_forward_as_integer(_p(out, np.complex128), _p(poly), C.c_size_t(N))
+    return out
+
+
+def fft_add_backward_as_torus(poly: np.ndarray, fourier: np.ndarray) -> None:
+    lib().orc_fft_add_backward_as_torus(_p(poly), _p(fourier, np.complex128), C.c_size_t(len(poly)))
+
+
+# ---------------------------------------------------------------- hot path
+def keyswitch(cts: np.ndarray, ksk: np.ndarray, n_in, n_out, base_log, level, native=False) -> np.ndarray:
+    num = cts.shape[0]
+    assert cts.shape[1] == n_in + 1 and ksk.size == n_in * level * (n_out + 1)
+    out = np.empty((num, n_out + 1), dtype=np.uint64)
+    lib(native).orc_keyswitch_batch(_p(out), _p(cts), _p(ksk), n_in, n_out, base_log, level, C.c_size_t(num))
+    return out
+
+
+def bsk_to_fourier(bsk: np.ndarray, n, k, level, N, native=False) -> np.ndarray:
+    assert bsk.size == n * level * (k + 1) ** 2 * N
+    out = np.empty(bsk.size // 2, dtype=np.complex128)
+    lib(native).orc_bsk_to_fourier(_p(out, np.complex128), _p(bsk), n, k, level, C.c_size_t(N))
+    return out
+
+
+def bootstrap(cts, luts, lut_idx, fbsk, n, k, N, base_log, level, nth=0, native=False) -> np.ndarray:
+    num = cts.shape[0]
+    assert cts.shape[1] == n + 1
+    luts = np.ascontiguousarray(luts.reshape(-1, (k + 1) * N))
+    out = np.empty((num, k * N + 1), dtype=np.uint64)
+    idx = None if lut_idx is None else _p(np.ascontiguousarray(lut_idx, dtype=np.uint64))
+    lib(native).orc_bootstrap_batch(
+        _p(out), _p(cts), _p(luts), idx, _p(fbsk, np.complex128), n, k, C.c_size_t(N),
+        base_log, level, C.c_size_t(num), C.c_size_t(nth))
+    return out
+
+
+def blind_rotate(cts, luts, lut_idx, fbsk, n, k, N, base_log, level) -> np.ndarray:
+    num = cts.shape[0]
+    luts = np.ascontiguousarray(luts.reshape(-1, (k + 1) * N))
+    out = np.empty((num, (k + 1) * N), dtype=np.uint64)
+    idx = None if lut_idx is None else _p(np.ascontiguousarray(lut_idx, dtype=np.uint64))
+    lib().orc_blind_rotate_batch(
+        _p(out), _p(cts), _p(luts), idx, _p(fbsk, np.complex128), n, k, C.c_size_t(N),
+        base_log, level, C.c_size_t(num))
+    return out
+
+
+# ---------------------------------------------------------------- harness
+def gen_binary_key(length: int, seed: int) -> np.ndarray:
+    key = np.empty(length, dtype=np.uint64)
+    lib().orc_gen_binary_key(_p(key), C.c_size_t(length), C.c_uint64(seed))
+    return key
+
+
+def lwe_encrypt(key: np.ndarray, plaintexts: np.ndarray, sigma: float, seed: int) -> np.ndarray:
+    n, num = len(key), len(plaintexts)
+    ct = np.empty((num, n + 1), dtype=np.uint64)
+    lib().orc_lwe_encrypt_batch(_p(ct), _p(key), _p(np.ascontiguousarray(plaintexts, dtype=np.uint64)),
+                                n, C.c_size_t(num), C.c_double(sigma), C.c_uint64(seed))
+    return ct
+
+
+def lwe_decrypt(key: np.ndarray, cts: np.ndarray) -> np.ndarray:
+    n, num = len(key), cts.shape[0]
+    assert cts.shape[1] == n + 1
+    pt = np.empty(num, dtype=np.uint64)
+    lib().orc_lwe_decrypt_batch(_p(pt), _p(np.ascontiguousarray(cts)), _p(key), n, C.c_size_t(num))
+    return pt
+
+
+def gen_ksk(key_in, key_out, base_log, level, sigma, seed) -> np.ndarray:
+    n_in, n_out = len(key_in), len(key_out)
+    ksk = np.empty(n_in * level * (n_out + 1), dtype=np.uint64)
+    lib().orc_gen_ksk(_p(ksk), _p(key_in), _p(key_out), n_in, n_out, base_log, level,
+                      C.c_double(sigma), C.c_uint64(seed))
+    return ksk
+
+
+def gen_bsk(lwe_key, glwe_key, k, N, base_log, level, sigma, seed) -> np.ndarray:
+    n = len(lwe_key)
+    assert len(glwe_key) == k * N
+    bsk = np.empty(n * level * (k + 1) ** 2 * N, dtype=np.uint64)
+    lib().orc_gen_bsk(_p(bsk), _p(lwe_key), _p(glwe_key), n, k, C.c_size_t(N), base_log, level,
+                      C.c_double(sigma), C.c_uint64(seed))
+    return bsk
