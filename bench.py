@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py — batched keyswitch + programmable bootstrap throughput (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload P2048] [--samples 16384]
+
+One "step" = one pass of the hot path (LWE keyswitch -> PBS) over one batch of synthetic
+ciphertexts per GPU.  Default workload = BASELINE.json configs[1]: 16 384 ciphertexts, 6-bit-class
+parameters k=1, N=2048 (n=742, l=1, b=23, l_ks=5, b_ks=3).  Ciphertexts are independent, so ranks
+shard them with no data-path collective ("weak" scaling: per-GPU batch fixed); the Fourier BSK and
+the KSK are prepared on rank 0 and broadcast once over NCCL.
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events, max over
+ranks); `e2e` = same metric through the runtime wrappers (memref_batched_*), host buffers,
+H2D/D2H inside the timed region; `roofline` = the fused PBS kernel against the FP64 peak measured
+live (and its HBM view); `cpu_baseline` = the oracle port on the host cores (bounded sample).
+`--impl reference` times the CPU restatement of the reference path on all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "batched_ks_pbs_throughput"
+UNIT = "PBS/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="P2048")
+    ap.add_argument("--samples", type=int, default=16384, help="ciphertexts per GPU per step")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(p, samples, n_gpus):
+    return {
+        "workload": f"batched keyswitch+PBS microbench, {samples} ciphertexts/GPU, params {p.name} "
+                    f"(n={p.n}, k={p.k}, N={p.N}, l={p.l}, b={p.b}, l_ks={p.l_ks}, b_ks={p.b_ks})",
+        "baseline_config": "configs[1]" if p.name == "P2048" and samples == 16384 else "custom",
+        "samples_per_gpu": samples,
+        "global_batch": samples * n_gpus,
+        "parallelism": f"ciphertext-sharded x{n_gpus}, no data-path collective",
+        "l2_policy": "inputs larger than L2 (ciphertext batch %.0f MB in + %.0f MB out per step)"
+                     % (samples * (p.big_n + 1) * 8 / 1e6, samples * (p.big_n + 1) * 8 / 1e6),
+    }
+
+
+# --------------------------------------------------------------------------- CPU legs (oracle)
+def cpu_oracle_rate(p, ks, cts_big, lut, budget_s, native=True):
+    """Times the oracle port (KS + PBS) on a bounded sample with all host threads."""
+    import oracle as orc
+
+    try:
+        orc.lib(native=native)
+    except Exception:
+        native = False
+    cores = orc.num_threads(native)
+    # calibrate with one ciphertext per thread
+    cal = cts_big[:cores]
+    t0 = time.perf_counter()
+    mid = orc.keyswitch(cal, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
+    orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
+    t_cal = time.perf_counter() - t0
+    rounds = max(1, int(budget_s / max(t_cal, 1e-3)))
+    count = min(len(cts_big), cores * rounds)
+    sample = cts_big[:count]
+    t0 = time.perf_counter()
+    mid = orc.keyswitch(sample, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
+    out = orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
+    dt = time.perf_counter() - t0
+    return {
+        "value": count / dt, "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": f"{count} ciphertexts (KS+PBS, {p.name}) in {dt:.2f} s, OpenMP x{cores}, "
+                  f"{'-march=native' if native else 'x86-64-v3'} build of oracle/tfhe_oracle.cpp",
+    }, out, count
+
+
+def run_reference(args):
+    """`--impl reference`: the CPU restatement of the reference path (concrete-cpu itself cannot be
+    built here: no Rust toolchain), all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from harness import KeySet, PARAMS, expand_lut, trivial_glwe
+    import oracle as orc
+
+    p = PARAMS[args.workload]
+    ks = KeySet(p, seed=42)
+    bits = min(p.msg_bits, 4)
+    try:
+        orc.lib(native=True)
+        native = True
+    except Exception:
+        native = False
+    cores = orc.num_threads(native)
+    per_step = cores * 2
+    rng = np.random.default_rng(42)
+    msgs = rng.integers(0, 1 << bits, per_step).astype(np.uint64)
+    cts = ks.encrypt_big(msgs, bits)
+    table = (np.arange(1 << bits) ** 2 % (1 << bits)).astype(np.uint64)
+    lut = trivial_glwe(expand_lut(table, p.N, bits), p.k)
+
+    def step():
+        mid = orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
+        return orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out = step()
+    dt = time.perf_counter() - t0
+    ok = bool(np.array_equal(ks.decrypt_big(out, bits), table[msgs]))
+    value = per_step * args.steps / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
+        "data": "synthetic (seed 42 keys/ciphertexts)",
+        "config": workload_config(p, args.samples, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"{per_step} ciphertexts per step (KS+PBS), OpenMP x{cores}; "
+                                   "concrete-cpu itself unavailable (no Rust toolchain)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "verified_decryptions": ok,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# --------------------------------------------------------------------------- GPU arm
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.proc = gpu, None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}",
+                 "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        sm, mx, reasons = [], [], set()
+        for ln in out.strip().splitlines():
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown",
+                                "sw_power_cap"), f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from concrete_b200 import Engine, as_u64
+    from concrete_b200.runtime import Runtime
+    from harness import KeySet, PARAMS, expand_lut, trivial_glwe
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = Engine(local)
+    lib = eng.lib
+    p = PARAMS[args.workload]
+    S = args.samples
+
+    # ---- synthetic encrypted inputs (seed 42), keys broadcast once over NCCL ----------------
+    ks = KeySet(p, seed=42, fourier_oracle=(rank == 0))
+    bits = min(p.msg_bits, 4)
+    rng = np.random.default_rng(42 + rank)
+    msgs = rng.integers(0, 1 << bits, S).astype(np.uint64)
+    cts_host = ks.encrypt_big(msgs, bits, seed=1000 + rank)
+    table = (np.arange(1 << bits) ** 2 % (1 << bits)).astype(np.uint64)
+    lut_poly = expand_lut(table, p.N, bits)
+    lut_host = trivial_glwe(lut_poly, p.k)
+    if rank == 0:
+        d_ksk = eng.upload_ksk(ks.ksk)
+        d_fbsk = eng.convert_bsk(ks.bsk, p.n, p.k, p.l, p.N)
+    else:
+        d_ksk = torch.empty(ks.ksk.size, dtype=torch.int64, device=eng.device)
+        d_fbsk = torch.empty(ks.bsk.size, dtype=torch.int64, device=eng.device)
+    if world > 1:
+        dist.broadcast(d_ksk, src=0)
+        dist.broadcast(d_fbsk, src=0)
+    d_cts = eng.to_device(cts_host)
+    d_lut = eng.to_device(lut_host)
+    d_lut_idx = torch.zeros(S, dtype=torch.int64, device=eng.device)
+    d_out = torch.empty((S, p.big_n + 1), dtype=torch.int64, device=eng.device)
+    d_mid = torch.empty((S, p.n + 1), dtype=torch.int64, device=eng.device)
+
+    def step():
+        eng.keyswitch_bootstrap(d_cts, d_ksk, d_fbsk, d_lut, d_lut_idx, p, out=d_out, ks_tmp=d_mid)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=eng.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = lib.concrete_b200_kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    launches = int(lib.concrete_b200_kernel_launches() - launches0)
+    ms_step = ms_total / args.steps
+    value = world * S / (ms_step * 1e-3)
+
+    # ---- dominant kernel alone (fused PBS) + keyswitch alone, CUDA events ----------------------
+    def time_call(fn, reps):
+        fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / reps
+
+    iota = eng.iota(S)
+    pbs_ms = time_call(lambda: eng.bootstrap(d_mid, d_lut, d_lut_idx, d_fbsk, p.n, p.k, p.N, p.b,
+                                             p.l, out=d_out, in_idx=iota, out_idx=iota), args.steps)
+    ks_ms = time_call(lambda: eng.keyswitch(d_cts, d_ksk, p.big_n, p.n, p.b_ks, p.l_ks, out=d_mid,
+                                            in_idx=iota, out_idx=iota), args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # FP64 FMA peak, measured live (MEASURED_PEAKS.json has no FP64 entry)
+    scratch = torch.empty(148 * 8 * 256, dtype=torch.float64, device=eng.device)
+    iters, blocks = 20000, 148 * 8
+    fp64_ms = time_call(lambda: lib.concrete_b200_fp64_peak(eng.stream, local, scratch.data_ptr(),
+                                                            blocks, iters), 3)
+    fp64_peak = blocks * 256 * iters * 32 / (fp64_ms * 1e-3) / 1e12
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    flops = S * p.pbs_flops()
+    bytes_alg = p.pbs_bytes(S)
+    achieved_tf = flops / (pbs_ms * 1e-3) / 1e12
+    roofline = {
+        "kernel": "pbs_kernel (fused blind rotation + sample extraction)",
+        "bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
+        "frac": achieved_tf / fp64_peak,
+        "peak_source": "FP64 FMA peak measured live by concrete_b200_fp64_peak (of measured)",
+        "flops_per_pbs": p.pbs_flops(), "launch_ms": pbs_ms,
+        "hbm": {"achieved": bytes_alg / (pbs_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": bytes_alg / (pbs_ms * 1e-3) / 1e9 / hbm_peak,
+                "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        "roofline_time_ms": max(flops / (fp64_peak * 1e12), bytes_alg / (hbm_peak * 1e9)) * 1e3,
+        "traffic": None,
+        "keyswitch": {"launch_ms": ks_ms, "u64_mac_per_s": S * p.ks_macs() / (ks_ms * 1e-3),
+                      "hbm_GBps": p.ks_bytes(S) / (ks_ms * 1e-3) / 1e9},
+    }
+
+    # ---- checker: decrypt a slice of the last step's output -----------------------------------
+    nchk = min(S, 512)
+    got = as_u64(d_out[:nchk])
+    verified = bool(np.array_equal(ks.decrypt_big(got, bits), table[msgs[:nchk]]))
+
+    # ---- e2e through the runtime wrappers, host buffers ---------------------------------------
+    e2e = None
+    if not args.no_e2e:
+        rt = Runtime(num_gpus=1, device_base=local)
+        ki, bi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk)
+        h_in = torch.from_numpy(cts_host.view(np.int64)).pin_memory().numpy().view(np.uint64)
+        h_mid = torch.empty((S, p.n + 1), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+        h_out = torch.empty((S, p.big_n + 1), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+
+        def e2e_step():
+            rt.batched_keyswitch(h_mid, h_in, p.l_ks, p.b_ks, p.big_n, p.n, ki)
+            rt.batched_bootstrap(h_out, h_mid, lut_poly, p.n, p.N, p.l, p.b, p.k, bi)
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            e2e_step()
+        barrier()
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3) / args.steps
+        ok2 = bool(np.array_equal(ks.decrypt_big(h_out[:nchk], bits), table[msgs[:nchk]]))
+        e2e = {
+            "value": world * S / (e2e_ms * 1e-3), "unit": UNIT,
+            "h2d_bytes_per_step": int(h_in.nbytes + h_mid.nbytes + lut_poly.nbytes),
+            "d2h_bytes_per_step": int(h_mid.nbytes + h_out.nbytes),
+            "ms_per_step": e2e_ms,
+            "api": "memref_batched_keyswitch_lwe_cuda_u64 + memref_batched_bootstrap_lwe_cuda_u64 "
+                   "(pinned host buffers; timed with the host clock around blocking calls)",
+            "verified_decryptions": ok2,
+        }
+        rt.close()
+
+    # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu, cpu_out, cnt = cpu_oracle_rate(p, ks, cts_host, lut_host, args.cpu_seconds)
+        cpu["verified_decryptions"] = bool(
+            np.array_equal(ks.decrypt_big(cpu_out, bits), table[msgs[:cnt]]))
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
+            "data": "synthetic (seed 42 keys and ciphertexts, valid encryptions)",
+            "config": workload_config(p, S, world),
+            "us_per_pbs": ms_step * 1e3 / S, "gpu_launches": launches,
+            "verified_decryptions": verified, "clocks": clocks, "roofline": roofline,
+            "e2e": e2e, "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -48,7 +48,8 @@ def _compile(src: str, verbose: bool) -> str:
     hdr_m = max(
         os.path.getmtime(os.path.join(CSRC, f)) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))
     )
-    hdr_m = max(hdr_m, os.path.getmtime(os.path.join(HERE, "..", "include", "concrete_b200.h")))
+    for h in os.listdir(os.path.join(HERE, "..", "include")):
+        hdr_m = max(hdr_m, os.path.getmtime(os.path.join(HERE, "..", "include", h)))
     if os.path.exists(obj) and os.path.getmtime(obj) > max(os.path.getmtime(src), hdr_m):
         return obj
     cmd = [_nvcc(), *NVCC_FLAGS, "-x", "cu", "-c", src, "-o", obj]

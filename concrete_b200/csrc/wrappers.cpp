@@ -1,0 +1,365 @@
+// wrappers.cpp — the runtime's batched-op dispatch, rebuilt on top of the C ABI.
+//
+// Same prototypes (MLIR memref ABI) and the same argument meaning / assertions as
+//   compilers/concrete-compiler/compiler/lib/Runtime/wrappers.cpp:70-106   (single ciphertext)
+//   ...:110-162  memref_batched_keyswitch_lwe_cuda_u64
+//   ...:164-256  memref_batched_bootstrap_lwe_cuda_u64
+//   ...:258-363  memref_batched_mapped_bootstrap_lwe_cuda_u64
+//   ...:745-849  memref_batched_{keyswitch,bootstrap,mapped_bootstrap}_lwe_u64 (CPU-named; here
+//                they run the same GPU path: the north star asks for no CPU fallback).
+// What changes relative to the reference implementation of these functions:
+//   * nothing is created per call: stream, device buffers, index arrays and the PBS scratch live
+//     in the RuntimeContext's per-GPU slot (the reference creates a stream, cudaMallocs inputs,
+//     outputs and indexes, and allocates + frees the PBS scratch on every call, :125-160,:176-255);
+//   * the trivial GLWE accumulator is assembled on the device (memset + strided copy of the
+//     N-word table) instead of on the host (:199-213);
+//   * batches are sharded over SDFG_NUM_GPUS devices with one host thread per device, contiguous
+//     split S_g = floor(S/G) (+1 for g < S mod G) — the reference hard-wires gpu 0 (:122,:177);
+//   * an extra fused entry point chains KS -> PBS without the host round trip.
+#include "runtime_context.h"
+#include <cassert>
+#include <cstdio>
+#include <cstring>
+#include <cuda_runtime.h>
+#include <functional>
+#include <thread>
+
+using mlir::concretelang::DevBuf;
+using mlir::concretelang::GpuSlot;
+using mlir::concretelang::RuntimeContext;
+
+namespace {
+
+#define W_CHECK(ans)                                                                     \
+  do {                                                                                   \
+    cudaError_t e__ = (ans);                                                             \
+    if (e__ != cudaSuccess) {                                                            \
+      std::fprintf(stderr, "Cuda error: %s %s %d\n", cudaGetErrorString(e__), __FILE__,  \
+                   __LINE__);                                                            \
+      std::abort();                                                                      \
+    }                                                                                    \
+  } while (0)
+
+void *ensure(DevBuf &b, uint64_t bytes, GpuSlot &s) {
+  if (b.cap >= bytes && b.ptr) return b.ptr;
+  if (b.ptr) {
+    cuda_synchronize_stream(s.stream, s.gpu);
+    cuda_drop(b.ptr, s.gpu);
+  }
+  uint64_t cap = bytes + bytes / 4 + 256;
+  b.ptr = cuda_malloc(cap, s.gpu);
+  b.cap = cap;
+  return b.ptr;
+}
+
+__global__ void k_fill_iota(uint64_t *p, uint32_t n) {
+  for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+    p[i] = i;
+}
+
+void *get_iota(GpuSlot &s, uint32_t n) {
+  if (s.iota_len >= n && s.iota.ptr) return s.iota.ptr;
+  uint32_t len = 1024;
+  while (len < n) len <<= 1;
+  ensure(s.iota, (uint64_t)len * 8, s);
+  W_CHECK(cudaSetDevice(s.gpu));
+  k_fill_iota<<<(len + 255) / 256, 256, 0, (cudaStream_t)s.stream>>>((uint64_t *)s.iota.ptr, len);
+  W_CHECK(cudaGetLastError());
+  s.iota_len = len;
+  return s.iota.ptr;
+}
+
+void ensure_pbs(GpuSlot &s, uint32_t k, uint32_t N, uint32_t l, uint32_t count) {
+  if (s.pbs_buffer && s.pbs_k == k && s.pbs_N == N && s.pbs_l == l && s.pbs_count >= count) return;
+  if (s.pbs_buffer) cleanup_cuda_programmable_bootstrap(s.stream, s.gpu, &s.pbs_buffer);
+  scratch_cuda_programmable_bootstrap_64(s.stream, s.gpu, &s.pbs_buffer, k, N, l, count, true);
+  s.pbs_k = k;
+  s.pbs_N = N;
+  s.pbs_l = l;
+  s.pbs_count = count;
+}
+
+// contiguous split of [0,total) over the active devices, one host thread per device
+// (GPUDFG.cpp:852-895; split rule helper_multi_gpu.cu:53-83)
+void for_each_shard(RuntimeContext *ctx, uint64_t total,
+                    const std::function<void(uint32_t gpu, uint64_t begin, uint64_t count)> &f) {
+  const uint64_t G = (uint64_t)std::max(1, std::min<int>(ctx->active_devices, (int)total));
+  const uint32_t base = (uint32_t)ctx->device_base;
+  if (G == 1) {
+    f(base, 0, total);
+    return;
+  }
+  std::vector<std::thread> threads;
+  uint64_t begin = 0;
+  for (uint64_t g = 0; g < G; ++g) {
+    uint64_t cnt = total / G + (g < total % G ? 1 : 0);
+    threads.emplace_back(f, base + (uint32_t)g, begin, cnt);
+    begin += cnt;
+  }
+  for (auto &t : threads) t.join();
+}
+
+// Upload `num_luts` tables of N words as trivial GLWE accumulators [(k+1)*N] (wrappers.cpp:199-213)
+void *upload_luts(GpuSlot &s, const uint64_t *tlu, uint64_t num_luts, uint64_t tlu_row_stride,
+                  uint32_t k, uint32_t N) {
+  const uint64_t glwe_words = (uint64_t)(k + 1) * N;
+  void *d = ensure(s.lut, num_luts * glwe_words * 8, s);
+  cuda_memset_async(d, 0, num_luts * glwe_words * 8, s.stream, s.gpu);
+  W_CHECK(cudaSetDevice(s.gpu));
+  W_CHECK(cudaMemcpy2DAsync((uint64_t *)d + (uint64_t)k * N, glwe_words * 8, tlu,
+                            tlu_row_stride * 8, (uint64_t)N * 8, num_luts,
+                            cudaMemcpyHostToDevice, (cudaStream_t)s.stream));
+  return d;
+}
+
+void bootstrap_impl(uint64_t *out, const uint64_t *ct0, uint64_t num_samples, uint64_t ct0_size1,
+                    uint64_t out_size1, const uint64_t *tlu, uint64_t num_luts,
+                    uint64_t tlu_row_stride, uint32_t input_lwe_dim, uint32_t poly_size,
+                    uint32_t level, uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
+                    RuntimeContext *context) {
+  for_each_shard(context, num_samples, [&](uint32_t gpu, uint64_t begin, uint64_t cnt) {
+    if (cnt == 0) return;
+    GpuSlot &s = context->slot(gpu);
+    const std::lock_guard<std::mutex> guard(s.mutex);
+    void *fbsk = context->get_bsk_gpu(input_lwe_dim, poly_size, level, glwe_dim, gpu, s.stream,
+                                      bsk_index);
+    void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
+    void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
+    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
+                             cnt * ct0_size1 * 8, s.stream, gpu);
+    void *d_lut, *d_lut_idx;
+    if (num_luts == 1) {
+      d_lut = upload_luts(s, tlu, 1, tlu_row_stride, glwe_dim, poly_size);
+      d_lut_idx = ensure(s.lut_idx, cnt * 8, s);
+      cuda_memset_async(d_lut_idx, 0, cnt * 8, s.stream, gpu);
+    } else {
+      // one table per sample: this shard's tables, indexes 0..cnt-1
+      d_lut = upload_luts(s, tlu + begin * tlu_row_stride, cnt, tlu_row_stride, glwe_dim,
+                          poly_size);
+      d_lut_idx = get_iota(s, (uint32_t)cnt);
+    }
+    void *iota = get_iota(s, (uint32_t)cnt);
+    ensure_pbs(s, glwe_dim, poly_size, level, (uint32_t)cnt);
+    cuda_programmable_bootstrap_lwe_ciphertext_vector_64(
+        s.stream, gpu, d_out, iota, d_lut, d_lut_idx, d_in, iota, fbsk, s.pbs_buffer,
+        input_lwe_dim, glwe_dim, poly_size, base_log, level, (uint32_t)cnt, 1, 1);
+    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
+    cuda_synchronize_stream(s.stream, gpu);
+  });
+}
+
+} // namespace
+
+extern "C" {
+
+// ---- context factory (the real runtime builds RuntimeContext from a ServerKeyset,
+//      lib/Runtime/context.cpp:32-57; host key buffers stay owned by the caller) ----------------
+void *concrete_b200_context_create(void) { return new RuntimeContext(); }
+void concrete_b200_context_destroy(void *ctx) { delete static_cast<RuntimeContext *>(ctx); }
+uint64_t concrete_b200_context_add_ksk(void *ctx, const uint64_t *data, uint64_t len) {
+  return static_cast<RuntimeContext *>(ctx)->add_keyswitch_key(data, len);
+}
+uint64_t concrete_b200_context_add_bsk(void *ctx, const uint64_t *data, uint64_t len) {
+  return static_cast<RuntimeContext *>(ctx)->add_bootstrap_key(data, len);
+}
+void concrete_b200_context_set_num_gpus(void *ctx, int n) {
+  RuntimeContext *c = static_cast<RuntimeContext *>(ctx);
+  if (n >= 1 && c->device_base + n <= c->num_devices) c->active_devices = n;
+}
+void concrete_b200_context_set_device_base(void *ctx, int base) {
+  RuntimeContext *c = static_cast<RuntimeContext *>(ctx);
+  if (base >= 0 && base + c->active_devices <= c->num_devices) c->device_base = base;
+}
+
+void memref_batched_keyswitch_lwe_cuda_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint32_t level, uint32_t base_log,
+    uint32_t input_lwe_dim, uint32_t output_lwe_dim, uint32_t ksk_index,
+    RuntimeContext *context) {
+  (void)out_allocated; (void)ct0_allocated; (void)out_stride0; (void)out_stride1;
+  (void)ct0_stride0; (void)ct0_stride1;
+  assert(out_size0 == ct0_size0);
+  assert(out_size1 == output_lwe_dim + 1);
+  assert(ct0_size1 == input_lwe_dim + 1);
+  uint64_t *out = out_aligned + out_offset;
+  const uint64_t *ct0 = ct0_aligned + ct0_offset;
+  for_each_shard(context, out_size0, [&](uint32_t gpu, uint64_t begin, uint64_t cnt) {
+    if (cnt == 0) return;
+    GpuSlot &s = context->slot(gpu);
+    const std::lock_guard<std::mutex> guard(s.mutex);
+    void *ksk = context->get_ksk_gpu(level, input_lwe_dim, output_lwe_dim, gpu, s.stream, ksk_index);
+    void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
+    void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
+    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
+                             cnt * ct0_size1 * 8, s.stream, gpu);
+    void *iota = get_iota(s, (uint32_t)cnt);
+    cuda_keyswitch_lwe_ciphertext_vector_64(s.stream, gpu, d_out, iota, d_in, iota, ksk,
+                                            input_lwe_dim, output_lwe_dim, base_log, level,
+                                            (uint32_t)cnt);
+    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
+    cuda_synchronize_stream(s.stream, gpu);
+  });
+}
+
+void memref_batched_bootstrap_lwe_cuda_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint64_t *tlu_allocated, uint64_t *tlu_aligned,
+    uint64_t tlu_offset, uint64_t tlu_size, uint64_t tlu_stride, uint32_t input_lwe_dim,
+    uint32_t poly_size, uint32_t level, uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
+    RuntimeContext *context) {
+  (void)out_allocated; (void)ct0_allocated; (void)tlu_allocated; (void)out_stride0;
+  (void)out_stride1; (void)ct0_stride0; (void)ct0_stride1; (void)tlu_stride;
+  assert(out_size0 == ct0_size0);
+  assert(out_size1 == glwe_dim * poly_size + 1);
+  assert(tlu_size == poly_size);
+  (void)tlu_size;
+  bootstrap_impl(out_aligned + out_offset, ct0_aligned + ct0_offset, out_size0, ct0_size1,
+                 out_size1, tlu_aligned + tlu_offset, 1, poly_size, input_lwe_dim, poly_size,
+                 level, base_log, glwe_dim, bsk_index, context);
+}
+
+void memref_batched_mapped_bootstrap_lwe_cuda_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint64_t *tlu_allocated, uint64_t *tlu_aligned,
+    uint64_t tlu_offset, uint64_t tlu_size0, uint64_t tlu_size1, uint64_t tlu_stride0,
+    uint64_t tlu_stride1, uint32_t input_lwe_dim, uint32_t poly_size, uint32_t level,
+    uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index, RuntimeContext *context) {
+  (void)out_allocated; (void)ct0_allocated; (void)tlu_allocated; (void)out_stride0;
+  (void)out_stride1; (void)ct0_stride0; (void)ct0_stride1; (void)tlu_stride0; (void)tlu_stride1;
+  assert(out_size0 == ct0_size0);
+  assert(out_size1 == glwe_dim * poly_size + 1);
+  assert((out_size0 == tlu_size0 || tlu_size0 == 1) && "Number of LUTs does not match batch size");
+  bootstrap_impl(out_aligned + out_offset, ct0_aligned + ct0_offset, out_size0, ct0_size1,
+                 out_size1, tlu_aligned + tlu_offset, tlu_size0, tlu_size1, input_lwe_dim,
+                 poly_size, level, base_log, glwe_dim, bsk_index, context);
+}
+
+// wrappers.cpp:70-106
+void memref_keyswitch_lwe_cuda_u64(uint64_t *out_allocated, uint64_t *out_aligned,
+                                   uint64_t out_offset, uint64_t out_size, uint64_t out_stride,
+                                   uint64_t *ct0_allocated, uint64_t *ct0_aligned,
+                                   uint64_t ct0_offset, uint64_t ct0_size, uint64_t ct0_stride,
+                                   uint32_t level, uint32_t base_log, uint32_t input_lwe_dim,
+                                   uint32_t output_lwe_dim, uint32_t ksk_index,
+                                   RuntimeContext *context) {
+  assert(out_stride == 1);
+  assert(ct0_stride == 1);
+  memref_batched_keyswitch_lwe_cuda_u64(out_allocated, out_aligned, out_offset, 1, out_size,
+                                        out_size, out_stride, ct0_allocated, ct0_aligned,
+                                        ct0_offset, 1, ct0_size, ct0_size, ct0_stride, level,
+                                        base_log, input_lwe_dim, output_lwe_dim, ksk_index,
+                                        context);
+}
+
+void memref_bootstrap_lwe_cuda_u64(uint64_t *out_allocated, uint64_t *out_aligned,
+                                   uint64_t out_offset, uint64_t out_size, uint64_t out_stride,
+                                   uint64_t *ct0_allocated, uint64_t *ct0_aligned,
+                                   uint64_t ct0_offset, uint64_t ct0_size, uint64_t ct0_stride,
+                                   uint64_t *tlu_allocated, uint64_t *tlu_aligned,
+                                   uint64_t tlu_offset, uint64_t tlu_size, uint64_t tlu_stride,
+                                   uint32_t input_lwe_dim, uint32_t poly_size, uint32_t level,
+                                   uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
+                                   RuntimeContext *context) {
+  memref_batched_bootstrap_lwe_cuda_u64(out_allocated, out_aligned, out_offset, 1, out_size,
+                                        out_size, out_stride, ct0_allocated, ct0_aligned,
+                                        ct0_offset, 1, ct0_size, ct0_size, ct0_stride,
+                                        tlu_allocated, tlu_aligned, tlu_offset, tlu_size,
+                                        tlu_stride, input_lwe_dim, poly_size, level, base_log,
+                                        glwe_dim, bsk_index, context);
+}
+
+// CPU-named wrappers (wrappers.cpp:745-849): same prototypes, same GPU path.
+void memref_batched_keyswitch_lwe_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint32_t level, uint32_t base_log,
+    uint32_t input_lwe_dim, uint32_t output_lwe_dim, uint32_t ksk_index,
+    RuntimeContext *context) {
+  memref_batched_keyswitch_lwe_cuda_u64(out_allocated, out_aligned, out_offset, out_size0,
+                                        out_size1, out_stride0, out_stride1, ct0_allocated,
+                                        ct0_aligned, ct0_offset, ct0_size0, ct0_size1,
+                                        ct0_stride0, ct0_stride1, level, base_log, input_lwe_dim,
+                                        output_lwe_dim, ksk_index, context);
+}
+
+void memref_batched_bootstrap_lwe_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint64_t *tlu_allocated, uint64_t *tlu_aligned,
+    uint64_t tlu_offset, uint64_t tlu_size, uint64_t tlu_stride, uint32_t input_lwe_dim,
+    uint32_t poly_size, uint32_t level, uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
+    RuntimeContext *context) {
+  memref_batched_bootstrap_lwe_cuda_u64(out_allocated, out_aligned, out_offset, out_size0,
+                                        out_size1, out_stride0, out_stride1, ct0_allocated,
+                                        ct0_aligned, ct0_offset, ct0_size0, ct0_size1,
+                                        ct0_stride0, ct0_stride1, tlu_allocated, tlu_aligned,
+                                        tlu_offset, tlu_size, tlu_stride, input_lwe_dim,
+                                        poly_size, level, base_log, glwe_dim, bsk_index, context);
+}
+
+void memref_batched_mapped_bootstrap_lwe_u64(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0,
+    uint64_t out_size1, uint64_t out_stride0, uint64_t out_stride1, uint64_t *ct0_allocated,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t ct0_stride0, uint64_t ct0_stride1, uint64_t *tlu_allocated, uint64_t *tlu_aligned,
+    uint64_t tlu_offset, uint64_t tlu_size0, uint64_t tlu_size1, uint64_t tlu_stride0,
+    uint64_t tlu_stride1, uint32_t input_lwe_dim, uint32_t poly_size, uint32_t level,
+    uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index, RuntimeContext *context) {
+  memref_batched_mapped_bootstrap_lwe_cuda_u64(
+      out_allocated, out_aligned, out_offset, out_size0, out_size1, out_stride0, out_stride1,
+      ct0_allocated, ct0_aligned, ct0_offset, ct0_size0, ct0_size1, ct0_stride0, ct0_stride1,
+      tlu_allocated, tlu_aligned, tlu_offset, tlu_size0, tlu_size1, tlu_stride0, tlu_stride1,
+      input_lwe_dim, poly_size, level, base_log, glwe_dim, bsk_index, context);
+}
+
+// Extension: KS -> PBS with the intermediate ciphertexts kept on the device (what the SDFG
+// runtime achieves per chunk, GPUDFG.cpp:1085,1209).  ct0: [S][big+1], out: [S][k*N+1].
+void memref_batched_keyswitch_bootstrap_lwe_cuda_u64(
+    uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size0, uint64_t out_size1,
+    uint64_t *ct0_aligned, uint64_t ct0_offset, uint64_t ct0_size0, uint64_t ct0_size1,
+    uint64_t *tlu_aligned, uint64_t tlu_offset, uint64_t tlu_size, uint32_t ks_level,
+    uint32_t ks_base_log, uint32_t big_lwe_dim, uint32_t small_lwe_dim, uint32_t ksk_index,
+    uint32_t poly_size, uint32_t level, uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
+    RuntimeContext *context) {
+  assert(out_size0 == ct0_size0);
+  assert(out_size1 == glwe_dim * poly_size + 1);
+  assert(ct0_size1 == big_lwe_dim + 1);
+  assert(tlu_size == poly_size);
+  (void)tlu_size;
+  uint64_t *out = out_aligned + out_offset;
+  const uint64_t *ct0 = ct0_aligned + ct0_offset;
+  const uint64_t *tlu = tlu_aligned + tlu_offset;
+  for_each_shard(context, out_size0, [&](uint32_t gpu, uint64_t begin, uint64_t cnt) {
+    if (cnt == 0) return;
+    GpuSlot &s = context->slot(gpu);
+    const std::lock_guard<std::mutex> guard(s.mutex);
+    void *ksk = context->get_ksk_gpu(ks_level, big_lwe_dim, small_lwe_dim, gpu, s.stream, ksk_index);
+    void *fbsk = context->get_bsk_gpu(small_lwe_dim, poly_size, level, glwe_dim, gpu, s.stream,
+                                      bsk_index);
+    void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
+    void *d_mid = ensure(s.ct_mid, cnt * (uint64_t)(small_lwe_dim + 1) * 8, s);
+    void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
+    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
+                             cnt * ct0_size1 * 8, s.stream, gpu);
+    void *d_lut = upload_luts(s, tlu, 1, poly_size, glwe_dim, poly_size);
+    void *d_lut_idx = ensure(s.lut_idx, cnt * 8, s);
+    cuda_memset_async(d_lut_idx, 0, cnt * 8, s.stream, gpu);
+    ensure_pbs(s, glwe_dim, poly_size, level, (uint32_t)cnt);
+    cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
+        s.stream, gpu, d_out, d_lut, d_lut_idx, d_in, ksk, fbsk, s.pbs_buffer, d_mid,
+        big_lwe_dim, small_lwe_dim, ks_base_log, ks_level, glwe_dim, poly_size, base_log, level,
+        (uint32_t)cnt);
+    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
+    cuda_synchronize_stream(s.stream, gpu);
+  });
+}
+
+} // extern "C"

@@ -59,6 +59,29 @@ SIGNATURES = {
     "concrete_b200_kernel_launches": (u64, []),
 }
 
+# runtime wrapper layer, include/concrete_b200_runtime.h (MLIR memref ABI; host pointers)
+_m2 = [vp, vp, u64, u64, u64, u64, u64]  # 2-D memref
+_m1 = [vp, vp, u64, u64, u64]            # 1-D memref
+SIGNATURES.update({
+    "concrete_b200_context_create": (vp, []),
+    "concrete_b200_context_destroy": (None, [vp]),
+    "concrete_b200_context_add_ksk": (u64, [vp, vp, u64]),
+    "concrete_b200_context_add_bsk": (u64, [vp, vp, u64]),
+    "concrete_b200_context_set_num_gpus": (None, [vp, C.c_int]),
+    "concrete_b200_context_set_device_base": (None, [vp, C.c_int]),
+    "memref_batched_keyswitch_lwe_cuda_u64": (None, _m2 + _m2 + [u32, u32, u32, u32, u32, vp]),
+    "memref_batched_bootstrap_lwe_cuda_u64": (None, _m2 + _m2 + _m1 + [u32, u32, u32, u32, u32, u32, vp]),
+    "memref_batched_mapped_bootstrap_lwe_cuda_u64": (None, _m2 + _m2 + _m2 + [u32, u32, u32, u32, u32, u32, vp]),
+    "memref_keyswitch_lwe_cuda_u64": (None, _m1 + _m1 + [u32, u32, u32, u32, u32, vp]),
+    "memref_bootstrap_lwe_cuda_u64": (None, _m1 + _m1 + _m1 + [u32, u32, u32, u32, u32, u32, vp]),
+    "memref_batched_keyswitch_lwe_u64": (None, _m2 + _m2 + [u32, u32, u32, u32, u32, vp]),
+    "memref_batched_bootstrap_lwe_u64": (None, _m2 + _m2 + _m1 + [u32, u32, u32, u32, u32, u32, vp]),
+    "memref_batched_mapped_bootstrap_lwe_u64": (None, _m2 + _m2 + _m2 + [u32, u32, u32, u32, u32, u32, vp]),
+    "memref_batched_keyswitch_bootstrap_lwe_cuda_u64": (
+        None, [vp, u64, u64, u64, vp, u64, u64, u64, vp, u64, u64] + [u32] * 10 + [vp]),
+    "concrete_b200_fp64_peak": (None, [vp, u32, vp, u32, u32]),
+})
+
 
 def library_path() -> str:
     return os.path.join(_HERE, "libconcrete_b200.so")

@@ -191,6 +191,10 @@ void cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
  * used by bench.py to report `gpu_launches`. */
 const char *concrete_b200_version(void);
 uint64_t concrete_b200_kernel_launches(void);
+/* FP64 FMA peak probe: `blocks` CTAs x 256 threads x iters x 16 DFMA (32 flop) per thread;
+ * bench.py times it with CUDA events for the roofline denominator. */
+void concrete_b200_fp64_peak(void *stream, uint32_t gpu_index, void *scratch, uint32_t blocks,
+                             uint32_t iters);
 
 #ifdef __cplusplus
 }

@@ -44,6 +44,12 @@ def main():
         torch.cuda.synchronize()
         got = as_u64(got)
         dist = torus_distance(got, ref_pbs)
+        lg = np.log2(dist + 1)
+        print("  dist log2 histogram:", np.histogram(lg, bins=[0, 20, 30, 40, 50, 55, 60, 62, 64])[0])
+        bad = np.argwhere(lg > 60)
+        print("  bad positions (sample, word):", bad[:10].tolist(), "count", len(bad))
+        for (si, wi) in bad[:4]:
+            print(f"    got={int(got[si, wi]):016x} ref={int(ref_pbs[si, wi]):016x}")
         dec = ks.decrypt_big(got, bits); dec_ref = ks.decrypt_big(ref_pbs, bits)
         print(f"  PBS decrypt ok: {np.array_equal(dec, table[msgs])} (oracle ok: {np.array_equal(dec_ref, table[msgs])}) "
               f"max|d|=2^{np.log2(dist.max()+1):.1f} sigma_fft=2^{np.log2(sigma_fft_ulp(p)):.1f} cpu {t_cpu:.2f}s", flush=True)
