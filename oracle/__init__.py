@@ -18,22 +18,44 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
+_LIB_NATIVE = None
 
 u64p = C.POINTER(C.c_uint64)
 
 
+def _native_name() -> str:
+    """-march=native objects must not travel between machines: key the file on the CPU flags."""
+    import hashlib
+
+    flags = ""
+    try:
+        with open("/proc/cpuinfo") as f:
+            for ln in f:
+                if ln.startswith("flags"):
+                    flags = ln
+                    break
+    except OSError:
+        pass
+    return "liboracle_native_%s.so" % hashlib.sha1(flags.encode()).hexdigest()[:10]
+
+
 def build(native: bool = False) -> str:
     """Compile the oracle with the committed Makefile; returns the .so path."""
-    target = "liboracle_native.so" if native else "liboracle.so"
-    subprocess.run(["make", "-C", _HERE, target], check=True, capture_output=True)
+    target = _native_name() if native else "liboracle.so"
+    args = ["make", "-C", _HERE, target]
+    if native:
+        args = ["make", "-C", _HERE, "native", f"NATIVE_SO={target}"]
+    subprocess.run(args, check=True, capture_output=True)
     return os.path.join(_HERE, target)
 
 
 def lib(native: bool = False):
-    global _LIB
+    global _LIB, _LIB_NATIVE
     if _LIB is not None and not native:
         return _LIB
-    path = os.path.join(_HERE, "liboracle_native.so" if native else "liboracle.so")
+    if _LIB_NATIVE is not None and native:
+        return _LIB_NATIVE
+    path = os.path.join(_HERE, _native_name() if native else "liboracle.so")
     src = os.path.join(_HERE, "tfhe_oracle.cpp")
     if not os.path.exists(path) or (
         os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(path)
@@ -54,7 +76,9 @@ def lib(native: bool = False):
     l.orc_from_torus.argtypes = [C.c_double]
     l.orc_num_threads.restype = C.c_int
     l.orc_set_num_threads.argtypes = [C.c_int]
-    if not native:
+    if native:
+        _LIB_NATIVE = l
+    else:
         _LIB = l
     return l
 
