@@ -29,6 +29,7 @@ namespace {
 // ------------------------------------------------------------------------------------------
 // Twiddle tables: tw[2^s + b] = exp(i*pi*(1 + 4*bitrev_s(b)) / 2^(s+2)), one per (device, LOGM)
 // ------------------------------------------------------------------------------------------
+void cb_w32_set_const_twiddles(const double2 *host_tw); // defined after pbs_w32.cuh
 std::mutex g_tw_mutex;
 std::map<std::pair<int, int>, double2 *> g_tw_cache;
 
@@ -56,6 +57,7 @@ const double2 *get_twiddles(int gpu, int logm) {
   double2 *d = nullptr;
   CB_CHECK(cudaMalloc(&d, M * sizeof(double2)));
   CB_CHECK(cudaMemcpy(d, h.data(), M * sizeof(double2), cudaMemcpyHostToDevice));
+  if (logm == 10) cb_w32_set_const_twiddles(h.data()); // current device == gpu
   g_tw_cache[key] = d;
   return d;
 }
@@ -121,6 +123,16 @@ struct PbsArgs {
   ulonglong2 *global_acc; // [gridDim.x][(K+1)*M] pairs, only when ACC_GLOBAL
   u32 n, base_log, level, num_samples, lut_count, lut_stride;
 };
+
+} // namespace
+#include "pbs_w32.cuh"
+namespace {
+
+void cb_w32_set_const_twiddles(const double2 *host_tw) {
+  CB_CHECK(cudaMemcpyToSymbol(w32::c_tw, host_tw, 32 * sizeof(double2)));
+}
+// the warp-per-polynomial kernels cover exactly this shape (BASELINE.json configs[1])
+inline bool use_w32(u32 k, u32 N, u32 level) { return k == 1 && N == 2048 && level == 1; }
 
 template <int K, int LOGN>
 __global__ void __launch_bounds__(PbsCfg<K, LOGN>::T, PbsCfg<K, LOGN>::MINB)
@@ -458,6 +470,34 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   if (lut_count == 0) lut_count = 1;
   if ((u64)(lut_count - 1) * lut_stride >= N)
     CB_PANIC("Cuda error (classical PBS): lut_count*lut_stride exceeds polynomial size");
+  if (use_w32(k, N, level)) {
+    PbsArgs a;
+    a.lwe_out = lwe_out;
+    a.out_idx = out_idx;
+    a.lut_vector = lut_vector;
+    a.lut_idx = lut_idx;
+    a.lwe_in = lwe_in;
+    a.in_idx = in_idx;
+    a.bsk = bsk;
+    a.tw = get_twiddles(gpu, 10);
+    a.global_acc = nullptr;
+    a.n = n;
+    a.base_log = base_log;
+    a.level = level;
+    a.num_samples = num_samples;
+    a.lut_count = lut_count;
+    a.lut_stride = lut_stride;
+    CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)w32::SMEM_BYTES));
+    int sms = 0;
+    CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+    const u32 ctas = (num_samples + w32::CPB - 1) / w32::CPB;
+    const u32 grid = std::min<u32>((u32)sms, ctas);
+    w32::pbs_kernel_w32<<<grid, w32::NTHREADS, w32::SMEM_BYTES, stream>>>(a);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
   const Variant &v = b->v;
   u32 grid = std::min<u32>((u32)b->grid_cap, num_samples);
   if (v.acc_global) {
@@ -501,10 +541,21 @@ void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_ho
                            src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
                            stream));
   const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
-  CB_CHECK(cudaFuncSetAttribute(v.convert, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                (int)v.fbuf_bytes));
   int sms = 0;
   CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  if (use_w32(k, N, level)) {
+    const size_t smem = w32::SMEM_TW + 4 * (size_t)w32::M * sizeof(double2);
+    CB_CHECK(cudaFuncSetAttribute(w32::bsk_convert_kernel_w32,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const u32 grid = (u32)std::min<size_t>((polys + 3) / 4, (size_t)sms * 2);
+    w32::bsk_convert_kernel_w32<<<grid, 128, smem, stream>>>(reinterpret_cast<double2 *>(dest),
+                                                             tw, polys);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
+  CB_CHECK(cudaFuncSetAttribute(v.convert, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.fbuf_bytes));
   const u32 grid = (u32)std::min<size_t>(polys, (size_t)sms * 8);
   v.convert<<<grid, v.T, v.fbuf_bytes, stream>>>(reinterpret_cast<double2 *>(dest), tw, polys);
   CB_CHECK(cudaGetLastError());
@@ -602,6 +653,17 @@ void cuda_fourier_polynomial_mul(void *stream, uint32_t gpu_index, void *input1,
     CB_PANIC("Cuda error (fourier mul): unsupported polynomial size %u", polynomial_size);
   const double2 *tw =
       get_twiddles(gpu_index, (int)std::lround(std::log2((double)polynomial_size)) - 1);
+  if (polynomial_size == 2048 && !std::getenv("CONCRETE_B200_GENERIC_FFT")) {
+    const size_t smem = w32::SMEM_TW + 4 * (size_t)w32::M * sizeof(double2);
+    CB_CHECK(cudaFuncSetAttribute(w32::poly_mul_kernel_w32,
+                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const u32 grid = std::min<u32>((total_polynomials + 3) / 4, 148 * 2);
+    w32::poly_mul_kernel_w32<<<grid, 128, smem, as_stream(stream)>>>(
+        (const double *)input1, (const double *)input2, (double *)output, tw, total_polynomials);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
   CB_CHECK(cudaFuncSetAttribute(v.polymul, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)v.fbuf_bytes));
   const u32 grid = std::min<u32>(total_polynomials, 148 * 8);

@@ -1,0 +1,371 @@
+// pbs_w32.cuh — "warp per polynomial" fast path of K3/K4 for N = 2048 (M = 1024 complex points),
+// k = 1, one decomposition level: the shape of BASELINE.json configs[1] (n=742, k=1, N=2048, l=1)
+// and of the reference's own benchmark (benchmark_pbs.cpp:388-403).
+//
+// Why this shape gets its own kernel: ncu on the generic kernel (profiles/r1_pbs_generic_*.txt)
+// shows it is bound by the L1/shared-memory data pipe (128 B/clk/SM), not by FP64: with 8 points
+// per thread an M = 1024 transform needs three shared-memory exchanges, the accumulator is read
+// twice and written once per CMUX, and register spills go through the same pipe.  Here
+//   * one WARP owns one polynomial of one ciphertext: 32 points per thread, the transform is
+//     5 register stages | ONE 16 KiB transpose through shared memory | 5 register stages, and
+//     the transpose needs only __syncwarp — no CTA barrier inside a transform;
+//   * the first 5 forward stages (last 5 inverse stages) use compile-time twiddles taken straight
+//     from the constant bank as DFMA operands; the other 31 per-lane twiddles come from a 16 KiB
+//     shared-memory table laid out [stage][sub-block][lane] (conflict-free LDS.128);
+//   * accumulator polynomial r is touched only by warp r, as (coef j, coef j+M) 16-byte pairs;
+//     the new value computed by the torus rounding of iteration i stays in registers and is the
+//     "own" operand of ACC*X^a - ACC of iteration i+1, so per CMUX the accumulator costs one
+//     rotated read, one read and one write of shared memory;
+//   * the two warps of a ciphertext meet once per CMUX (named barrier, 64 threads) to swap the
+//     cross terms X_r * G[r][1-r] of the external product;
+//   * the Fourier key is scaled by 1/M (not 2^-64/M), so the inverse transform delivers the
+//     result already in units of 2^-64 and torus rounding is 3 DADD + 1 F2I.
+// Restates the same reference code as pbs.cu (bootstrap.rs:250-368, ggsw.rs:481-602).
+#pragma once
+
+namespace w32 {
+
+constexpr int LOGM = 10, M = 1024, N = 2048;
+constexpr int CPB = 3;                    // ciphertexts per CTA (2 warps each)
+constexpr int NTHREADS = 64 * CPB;
+constexpr int ACC_PAIRS = 2 * M;          // two polynomials, M pairs each
+constexpr size_t SMEM_TW = 31 * 32 * sizeof(double2);                    // 15 872 B
+constexpr size_t SMEM_PER_CT = (size_t)ACC_PAIRS * 16 + 2 * (size_t)M * 16; // 64 KiB
+constexpr size_t SMEM_BYTES = SMEM_TW + CPB * SMEM_PER_CT;
+
+// tw[2^s + b], s = 0..4 (31 entries at indices 1..31): compile-time indexed -> c[bank] operands
+__constant__ double2 c_tw[32];
+
+__device__ __forceinline__ int swz(int idx, int key) { return idx ^ (key & 7); }
+
+// ---- register passes -------------------------------------------------------------------------
+// Pass 1 (forward stages 0..4): thread holds j = lane + 32*p, in-thread bits are j[9:5] = p.
+__device__ __forceinline__ void fwd_pass1(double2 (&x)[32]) {
+#pragma unroll
+  for (int s = 0; s < 5; ++s) {
+    const int rho = 4 - s;
+#pragma unroll
+    for (int u = 0; u < (1 << s); ++u) {
+      const double2 w = c_tw[(1 << s) + u];
+#pragma unroll
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo;
+        cbfft::bfly_ct(x[p], x[p | (1 << rho)], w);
+      }
+    }
+  }
+}
+// Pass 2 (forward stages 5..9): thread holds j = 32*lane + p, in-thread bits are j[4:0] = p.
+// tws[((2^(s-5) - 1) + u) * 32 + lane] = tw[2^s + (lane << (s-5)) + u].
+__device__ __forceinline__ void fwd_pass2(double2 (&x)[32], const double2 *tws, int lane) {
+#pragma unroll
+  for (int s2 = 0; s2 < 5; ++s2) {
+    const int rho = 4 - s2;
+#pragma unroll
+    for (int u = 0; u < (1 << s2); ++u) {
+      const double2 w = tws[(((1 << s2) - 1) + u) * 32 + lane];
+#pragma unroll
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo;
+        cbfft::bfly_ct(x[p], x[p | (1 << rho)], w);
+      }
+    }
+  }
+}
+__device__ __forceinline__ void inv_pass2(double2 (&x)[32], const double2 *tws, int lane) {
+#pragma unroll
+  for (int s2 = 4; s2 >= 0; --s2) {
+    const int rho = 4 - s2;
+#pragma unroll
+    for (int u = 0; u < (1 << s2); ++u) {
+      const double2 w = tws[(((1 << s2) - 1) + u) * 32 + lane];
+#pragma unroll
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo;
+        cbfft::bfly_gs(x[p], x[p | (1 << rho)], w);
+      }
+    }
+  }
+}
+__device__ __forceinline__ void inv_pass1(double2 (&x)[32]) {
+#pragma unroll
+  for (int s = 4; s >= 0; --s) {
+    const int rho = 4 - s;
+#pragma unroll
+    for (int u = 0; u < (1 << s); ++u) {
+      const double2 w = c_tw[(1 << s) + u];
+#pragma unroll
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo;
+        cbfft::bfly_gs(x[p], x[p | (1 << rho)], w);
+      }
+    }
+  }
+}
+
+// transpose between the two register layouts through a 16 KiB buffer owned by this warp
+__device__ __forceinline__ void xchg_1to2(double2 (&x)[32], double2 *buf, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) buf[swz(lane + 32 * p, p)] = x[p];
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) x[p] = buf[swz(32 * lane + p, lane)];
+}
+__device__ __forceinline__ void xchg_2to1(double2 (&x)[32], double2 *buf, int lane) {
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) buf[swz(32 * lane + p, lane)] = x[p];
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) x[p] = buf[swz(lane + 32 * p, p)];
+}
+
+// In: x[p] = z_{lane + 32p}.  Out: x[p] = F_{q = 32*lane + p}.
+__device__ __forceinline__ void forward(double2 (&x)[32], double2 *buf, const double2 *tws,
+                                        int lane) {
+  fwd_pass1(x);
+  xchg_1to2(x, buf, lane);
+  fwd_pass2(x, tws, lane);
+}
+// In: x[p] = F_{32*lane + p}.  Out: x[p] = M * z_{lane + 32p} (unnormalised).
+__device__ __forceinline__ void inverse(double2 (&x)[32], double2 *buf, const double2 *tws,
+                                        int lane) {
+  inv_pass2(x, tws, lane);
+  xchg_2to1(x, buf, lane);
+  inv_pass1(x);
+}
+
+__device__ __forceinline__ void load_tws(double2 *tws, const double2 *__restrict__ tw, int tid,
+                                         int nthreads) {
+  for (int e = tid; e < 31 * 32; e += nthreads) {
+    const int row = e >> 5, lane = e & 31;
+    int s2 = 0;
+    while (((1 << (s2 + 1)) - 1) <= row) ++s2;
+    const int u = row - ((1 << s2) - 1);
+    tws[e] = tw[(1 << (s2 + 5)) + (lane << s2) + u];
+  }
+}
+
+// round(v) mod 2^64 for v already in units of 2^-64 (torus/mod.rs:72-78 with the 2^64 folded in)
+__device__ __forceinline__ u64 from_torus_scaled(double v) {
+  const double C = 1.5 * 4503599627370496.0 * 18446744073709551616.0; // 1.5 * 2^52 * 2^64
+  const double r = (v + C) - C;                                        // nearest multiple of 2^64
+  return (u64)__double2ll_rn(v - r);
+}
+
+// closest_representable + the single balanced digit of a one-level decomposition, from the high
+// word only (base_log <= 31, so every bit that matters lives in bits 63..32):
+// decomposer.rs:23-47 then iter.rs:121-133 with state >> base_log == 0.
+__device__ __forceinline__ int digit_l1(u32 hi, u32 base_log) {
+  u32 r = ((hi >> (31 - base_log)) + 1) >> 1;
+  r &= (1u << base_log) - 1;
+  const u32 carry = ((r - 1) & r) >> (base_log - 1);
+  return (int)(r - (carry << base_log));
+}
+
+// ---- K3 fast path ------------------------------------------------------------------------------
+__global__ void __launch_bounds__(NTHREADS, 1) pbs_kernel_w32(const PbsArgs a) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *tws = reinterpret_cast<double2 *>(smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ct = warp >> 1, r = warp & 1;
+  unsigned char *base = smem + SMEM_TW + (size_t)ct * SMEM_PER_CT;
+  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(base) + r * M; // this warp's polynomial
+  double2 *buf_own = reinterpret_cast<double2 *>(base + (size_t)ACC_PAIRS * 16) + r * M;
+  double2 *buf_oth = reinterpret_cast<double2 *>(base + (size_t)ACC_PAIRS * 16) + (1 - r) * M;
+  const int bar_id = 1 + ct;
+
+  load_tws(tws, a.tw, tid, NTHREADS);
+  __syncthreads();
+
+  const u32 n = a.n, base_log = a.base_log;
+  const size_t out_size = (size_t)N + 1;
+  const double2 *__restrict__ gown = a.bsk + (size_t)(r * 2 + r) * M + lane;
+  const double2 *__restrict__ goth = a.bsk + (size_t)(r * 2 + (1 - r)) * M + lane;
+
+  for (u32 sample = blockIdx.x * CPB + ct; sample < a.num_samples; sample += gridDim.x * CPB) {
+    const u64 *lwe = a.lwe_in + a.in_idx[sample] * (u64)(n + 1);
+    const u32 b_hat = modulus_switch(__ldg(&lwe[n]), LOGM + 2);
+    const u64 *lut = a.lut_vector + a.lut_idx[sample] * (u64)(2 * N) + (size_t)r * N;
+
+    // ACC_r <- LUT_r * X^(-b_hat); own[] keeps this thread's pairs in registers
+    u64 own_re[32], own_im[32];
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const int j = lane + 32 * p;
+      {
+        const u32 u = (j + b_hat) & (2 * N - 1);
+        const u64 w = __ldg(&lut[u & (N - 1)]);
+        own_re[p] = (u < (u32)N) ? w : (u64)0 - w;
+      }
+      {
+        const u32 u = (j + M + b_hat) & (2 * N - 1);
+        const u64 w = __ldg(&lut[u & (N - 1)]);
+        own_im[p] = (u < (u32)N) ? w : (u64)0 - w;
+      }
+      acc[j] = make_ulonglong2(own_re[p], own_im[p]);
+    }
+    __syncwarp();
+
+    u32 a_next = modulus_switch(__ldg(&lwe[0]), LOGM + 2);
+#pragma unroll 1
+    for (u32 i = 0; i < n; ++i) {
+      const u32 a_hat = a_next;
+      if (i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), LOGM + 2);
+      if (a_hat != 0) { // X^0 - 1 = 0: the CMUX adds nothing (bootstrap.rs:287)
+
+      // ct1 = ACC*X^a - ACC, closest_representable, signed digit (l = 1) -> doubles
+      double2 x[32];
+#pragma unroll
+      for (int p = 0; p < 32; ++p) {
+        const int j = lane + 32 * p;
+        const u32 s = (u32)(j - (int)a_hat) & (2 * N - 1);
+        const u32 q = s >> LOGM;
+        const ulonglong2 src = acc[s & (M - 1)];
+        const u64 ra = (q & 1) ? src.y : src.x;
+        const u64 rb = (q & 1) ? src.x : src.y;
+        // (-i)^q * (A + iB): negate re for q in {2,3}, im for q in {1,2}
+        const u64 m_re = (u64)0 - (u64)(q >> 1);
+        const u64 m_im = (u64)0 - (u64)(((q + 1) >> 1) & 1);
+        const u64 c_re = ((ra ^ m_re) - m_re) - own_re[p];
+        const u64 c_im = ((rb ^ m_im) - m_im) - own_im[p];
+        x[p].x = __int2double_rn(digit_l1((u32)(c_re >> 32), base_log));
+        x[p].y = __int2double_rn(digit_l1((u32)(c_im >> 32), base_log));
+      }
+
+      forward(x, buf_own, tws, lane);
+
+      // external product: cross term to the partner warp, own term in place
+      const double2 *__restrict__ g0 = gown + (size_t)i * 4 * M;
+      const double2 *__restrict__ g1 = goth + (size_t)i * 4 * M;
+      __syncwarp(); // every lane is done reading buf_own (transpose) before it is overwritten
+#pragma unroll
+      for (int p = 0; p < 32; ++p) {
+        const double2 wo = __ldg(&g1[p * 32]);
+        double2 cr;
+        cr.x = fma(x[p].x, wo.x, -x[p].y * wo.y);
+        cr.y = fma(x[p].x, wo.y, x[p].y * wo.x);
+        buf_own[swz(32 * lane + p, lane)] = cr;
+        const double2 w = __ldg(&g0[p * 32]);
+        const double re = fma(x[p].x, w.x, -x[p].y * w.y);
+        const double im = fma(x[p].x, w.y, x[p].y * w.x);
+        x[p].x = re;
+        x[p].y = im;
+      }
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+#pragma unroll
+      for (int p = 0; p < 32; ++p) {
+        const double2 o = buf_oth[swz(32 * lane + p, lane)];
+        x[p].x += o.x;
+        x[p].y += o.y;
+      }
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory"); // partner done with buf_own
+
+      inverse(x, buf_own, tws, lane);
+
+      // ACC += round(x) ; the new value stays in registers as next iteration's "own" (own[] is
+      // dead during the transforms, so it is re-read here instead of being carried through them)
+#pragma unroll
+      for (int p = 0; p < 32; ++p) {
+        const ulonglong2 o = acc[lane + 32 * p];
+        own_re[p] = o.x + from_torus_scaled(x[p].x);
+        own_im[p] = o.y + from_torus_scaled(x[p].y);
+        acc[lane + 32 * p] = make_ulonglong2(own_re[p], own_im[p]);
+      }
+      __syncwarp();
+      } // a_hat != 0
+    }
+
+    // sample extraction (glwe_sample_extraction.rs:90-165): warp 0 owns the mask polynomial,
+    // warp 1 the body polynomial
+    for (u32 li = 0; li < a.lut_count; ++li) {
+      const u32 nth = li * a.lut_stride;
+      u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
+      if (r == 0) {
+        for (int xo = lane; xo < N; xo += 32) {
+          const int src = (xo <= (int)nth) ? ((int)nth - xo) : (N + (int)nth - xo);
+          const ulonglong2 pr = acc[src & (M - 1)];
+          const u64 v = (src < M) ? pr.x : pr.y;
+          out[xo] = (xo <= (int)nth) ? v : (u64)0 - v;
+        }
+      } else if (lane == 0) {
+        const ulonglong2 pr = acc[nth & (M - 1)];
+        out[N] = (nth < (u32)M) ? pr.x : pr.y;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// ---- K4 fast path: one warp per key polynomial, output in the [p][lane] order pbs_kernel_w32
+// reads, scaled by 1/M only (see header).
+__global__ void __launch_bounds__(128) bsk_convert_kernel_w32(double2 *bsk,
+                                                              const double2 *__restrict__ tw,
+                                                              size_t num_polys) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *tws = reinterpret_cast<double2 *>(smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double2 *buf = reinterpret_cast<double2 *>(smem + SMEM_TW) + warp * M;
+  load_tws(tws, tw, tid, blockDim.x);
+  __syncthreads();
+  const size_t wpb = blockDim.x >> 5;
+  for (size_t poly = blockIdx.x * wpb + warp; poly < num_polys; poly += gridDim.x * wpb) {
+    const u64 *src = reinterpret_cast<const u64 *>(bsk + poly * M);
+    double2 x[32];
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const int j = lane + 32 * p;
+      x[p].x = __ll2double_rn((i64)src[j]) * (1.0 / (double)M);
+      x[p].y = __ll2double_rn((i64)src[j + M]) * (1.0 / (double)M);
+    }
+    __syncwarp(); // every read of this polynomial precedes the in-place writes
+    forward(x, buf, tws, lane);
+    double2 *dst = bsk + poly * M;
+#pragma unroll
+    for (int p = 0; p < 32; ++p) dst[p * 32 + lane] = x[p];
+  }
+}
+
+// FFT test hook on the warp-level transform (N = 2048 only)
+__global__ void __launch_bounds__(128) poly_mul_kernel_w32(const double *in1, const double *in2,
+                                                           double *out,
+                                                           const double2 *__restrict__ tw,
+                                                           u32 total) {
+  extern __shared__ __align__(16) unsigned char smem[];
+  double2 *tws = reinterpret_cast<double2 *>(smem);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  double2 *buf = reinterpret_cast<double2 *>(smem + SMEM_TW) + warp * M;
+  load_tws(tws, tw, tid, blockDim.x);
+  __syncthreads();
+  const u32 wpb = blockDim.x >> 5;
+  for (u32 poly = blockIdx.x * wpb + warp; poly < total; poly += gridDim.x * wpb) {
+    double2 x[32], y[32];
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const int j = lane + 32 * p;
+      x[p] = make_double2(in1[(size_t)poly * N + j], in1[(size_t)poly * N + j + M]);
+    }
+    forward(x, buf, tws, lane);
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const int j = lane + 32 * p;
+      y[p] = make_double2(in2[(size_t)poly * N + j], in2[(size_t)poly * N + j + M]);
+    }
+    forward(y, buf, tws, lane);
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const double2 u = x[p], v = y[p];
+      x[p] = make_double2(u.x * v.x - u.y * v.y, u.x * v.y + u.y * v.x);
+    }
+    inverse(x, buf, tws, lane);
+#pragma unroll
+    for (int p = 0; p < 32; ++p) {
+      const int j = lane + 32 * p;
+      out[(size_t)poly * N + j] = x[p].x * (1.0 / (double)M);
+      out[(size_t)poly * N + j + M] = x[p].y * (1.0 / (double)M);
+    }
+  }
+}
+
+} // namespace w32

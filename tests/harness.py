@@ -88,3 +88,45 @@ def sigma_fft_ulp(p: TfheParams) -> float:
     external_product_glwe.rs:62-89 summed over n iterations)."""
     import math
     return math.sqrt(p.n * 2 ** 19.42 * p.l * (p.k + 1)) * (2 ** p.b) * p.N
+
+
+def phase_distance(ks: "KeySet", a: np.ndarray, b: np.ndarray) -> np.ndarray:
+    """|phase(a) - phase(b)| per ciphertext under the big key, in units of 2^-64.
+
+    Why phases and not ciphertext words: from the second CMUX on, an f64 rounding difference of
+    a few ulp in the accumulator flips the signed digit of any coefficient that sits next to a
+    rounding boundary of closest_representable, and one flipped digit adds +-1 x (a uniformly
+    random BSK mask row) to the output mask.  Ciphertext WORDS of two f64 implementations (or of
+    concrete-cpu on two machines) therefore differ by ~2^63 while the PHASE
+    (b - <a, s>, i.e. plaintext + noise) stays within the PBS noise (see phase_tolerance).  The
+    word-level tolerance is checked where it is meaningful: one external product from an
+    identical accumulator (tests/test_gpu_parity.py::test_external_product_word_tolerance)."""
+    pa = orc.lwe_decrypt(ks.sk_glwe, np.ascontiguousarray(a))
+    pb = orc.lwe_decrypt(ks.sk_glwe, np.ascontiguousarray(b))
+    return torus_distance(pa, pb)
+
+
+def sigma_round_ulp(p: TfheParams) -> float:
+    """Std of the decomposition-rounding noise a full PBS adds to the phase, units of 2^-64:
+    every ct1 coefficient is rounded to a multiple of the granule g = 2^(64 - b*l) (error uniform
+    in +-g/2, variance g^2/12) and reaches the phase through <mask, key> (k*N/2 + 1 terms), once
+    per CMUX (noise model: backends/concrete-cpu/noise-model/src/gaussian_noise/noise/
+    external_product_glwe.rs:62-89, first term)."""
+    import math
+    g = 2.0 ** (64 - p.b * p.l)
+    return math.sqrt(p.n * (p.k * p.N / 2 + 1) / 12.0) * g
+
+
+def phase_tolerance(p: TfheParams) -> float:
+    """Gate for |phase(ours) - phase(oracle)| after a FULL PBS, in units of 2^-64.
+
+    Two f64 implementations agree word for word only until the first signed digit flips at a
+    rounding boundary of closest_representable (an accumulator difference of a few ulp is
+    enough).  From that CMUX on the two runs hold different — equally valid — roundings of their
+    accumulators, i.e. independent realisations of the PBS's own decomposition-rounding noise, so
+    their phases differ like two noise samples: std sqrt(2) * sigma_round on top of the FFT
+    error.  Gate = 8 * sqrt(sigma_fft^2 + sigma_round^2).  P2048: 2^52.5, i.e. 1% of a 4-bit
+    message step (2^59).  The tight word-level gate (8 * sigma_fft) is applied where it is
+    meaningful: one CMUX from an identical accumulator."""
+    import math
+    return 8.0 * math.sqrt(sigma_fft_ulp(p) ** 2 + sigma_round_ulp(p) ** 2)
