@@ -126,6 +126,7 @@ struct PbsArgs {
 
 } // namespace
 #include "pbs_w32.cuh"
+#include "pbs_w32_v2.cuh"
 namespace {
 
 void cb_w32_set_const_twiddles(const double2 *host_tw) {
@@ -487,13 +488,24 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     a.num_samples = num_samples;
     a.lut_count = lut_count;
     a.lut_stride = lut_stride;
-    CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  (int)w32::SMEM_BYTES));
     int sms = 0;
     CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
-    const u32 ctas = (num_samples + w32::CPB - 1) / w32::CPB;
-    const u32 grid = std::min<u32>((u32)sms, ctas);
-    w32::pbs_kernel_w32<<<grid, w32::NTHREADS, w32::SMEM_BYTES, stream>>>(a);
+    static const bool use_v1 = std::getenv("CONCRETE_B200_W32_V1") != nullptr;
+    if (use_v1) {
+      CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)w32::SMEM_BYTES));
+      const u32 ctas = (num_samples + w32::CPB - 1) / w32::CPB;
+      const u32 grid = std::min<u32>((u32)sms, ctas);
+      w32::pbs_kernel_w32<<<grid, w32::NTHREADS, w32::SMEM_BYTES, stream>>>(a);
+    } else {
+      CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32v2,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)w32::SMEM_BYTES2));
+      const u32 ctas = (num_samples + w32::CPB2 - 1) / w32::CPB2;
+      const u32 grid = std::min<u32>((u32)sms, ctas);
+      w32::pbs_kernel_w32v2<<<grid, w32::NTHREADS2, w32::SMEM_BYTES2, stream>>>(a);
+    }
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
     return;
