@@ -102,6 +102,25 @@ __device__ __forceinline__ void tmem_wait_st() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// release the stage; the last of the 2*n_active warps refills it with the next GGSW
+__device__ __forceinline__ void release_stage(V2Ctrl *ctrl, unsigned char *stage,
+                                              const double2 *bsk, int lane, u32 n_active, u32 i,
+                                              u32 n, bool more_rounds) {
+  __syncwarp();
+  if (lane == 0) {
+    __threadfence_block();
+    const u32 prev = atomicAdd(&ctrl->released, 1u);
+    if (prev + 1 == 2 * n_active) {
+      ctrl->released = 0;
+      __threadfence_block();
+      if (i + 1 < n)
+        issue_stage(stage, bsk, i + 1, &ctrl->full_bar);
+      else if (more_rounds)
+        issue_stage(stage, bsk, 0, &ctrl->full_bar);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a) {
   extern __shared__ __align__(128) unsigned char smem[];
   double2 *tws = reinterpret_cast<double2 *>(smem);
@@ -191,8 +210,12 @@ __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a
       const u32 a_hat = a_next;
       if (i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), LOGM + 2);
 
-      double2 x[32];
-      if (a_hat != 0) {
+      if (a_hat == 0) { // X^0 - 1 = 0: no CMUX (bootstrap.rs:287); still take part in the stage
+        mbar_wait(&ctrl->full_bar, full_parity);
+        full_parity ^= 1;
+        release_stage(ctrl, stage, a.bsk, lane, n_active, i, n, more_rounds);
+      } else {
+        double2 x[32];
 #pragma unroll
         for (int p = 0; p < 32; ++p) {
           const int j = lane + 32 * p;
@@ -209,13 +232,11 @@ __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a
           x[p].y = __int2double_rn(digit_l1((u32)(c_im >> 32), base_log));
         }
         forward(x, buf, tws, lane);
-      }
 
-      // GGSW i is in the stage once the TMA transaction completes
-      mbar_wait(&ctrl->full_bar, full_parity);
-      full_parity ^= 1;
+        // GGSW i is in the stage once the TMA transaction completes
+        mbar_wait(&ctrl->full_bar, full_parity);
+        full_parity ^= 1;
 
-      if (a_hat != 0) {
         __syncwarp(); // transpose reads of buf are done in every lane
 #pragma unroll
         for (int p = 0; p < 32; ++p) {
@@ -230,24 +251,8 @@ __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a
           x[p].x = re;
           x[p].y = im;
         }
-      }
+        release_stage(ctrl, stage, a.bsk, lane, n_active, i, n, more_rounds);
 
-      // release the stage; the last of the 2*n_active warps refills it with the next GGSW
-      __syncwarp();
-      if (lane == 0) {
-        __threadfence_block();
-        const u32 prev = atomicAdd(&ctrl->released, 1u);
-        if (prev + 1 == 2 * n_active) {
-          ctrl->released = 0;
-          __threadfence_block();
-          if (i + 1 < n)
-            issue_stage(stage, a.bsk, i + 1, &ctrl->full_bar);
-          else if (more_rounds)
-            issue_stage(stage, a.bsk, 0, &ctrl->full_bar);
-        }
-      }
-
-      if (a_hat != 0) {
         asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
 #pragma unroll
         for (int p = 0; p < 32; ++p) {
