@@ -122,11 +122,14 @@ struct PbsArgs {
   const double2 *tw;
   ulonglong2 *global_acc; // [gridDim.x][(K+1)*M] pairs, only when ACC_GLOBAL
   u32 n, base_log, level, num_samples, lut_count, lut_stride;
+  u32 cpb_active; // w32 v2 experiment: ciphertexts per CTA actually used (1..4)
+  u32 skew_ns; // w32 v2: start-up phase offset between the ciphertexts of a CTA
 };
 
 } // namespace
 #include "pbs_w32.cuh"
 #include "pbs_w32_v2.cuh"
+#include "pbs_w32_v3.cuh"
 namespace {
 
 void cb_w32_set_const_twiddles(const double2 *host_tw) {
@@ -141,7 +144,7 @@ pbs_kernel(const PbsArgs a) {
   using C = PbsCfg<K, LOGN>;
   constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
   constexpr int GS = K + 1;
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *fbuf = reinterpret_cast<double2 *>(smem);
   ulonglong2 *acc;
   unsigned short *s_ahat;
@@ -286,7 +289,7 @@ __global__ void __launch_bounds__(PbsCfg<K, LOGN>::T)
 bsk_convert_kernel(double2 *bsk, const double2 *__restrict__ tw, size_t num_polys) {
   using C = PbsCfg<K, LOGN>;
   constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, P = C::P, T = C::T;
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *fbuf = reinterpret_cast<double2 *>(smem);
   const int t = threadIdx.x;
   for (size_t poly = blockIdx.x; poly < num_polys; poly += gridDim.x) {
@@ -316,7 +319,7 @@ poly_mul_kernel(const double *in1, const double *in2, double *out,
                 const double2 *__restrict__ tw, u32 total) {
   using C = PbsCfg<K, LOGN>;
   constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *fbuf = reinterpret_cast<double2 *>(smem);
   const int t = threadIdx.x;
   for (u32 poly = blockIdx.x; poly < total; poly += gridDim.x) {
@@ -488,23 +491,35 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     a.num_samples = num_samples;
     a.lut_count = lut_count;
     a.lut_stride = lut_stride;
+    static const char *skew_env = std::getenv("CONCRETE_B200_SKEW_NS");
+    a.skew_ns = skew_env ? (u32)std::atoi(skew_env) : 0;
+    static const char *cpb_env = std::getenv("CONCRETE_B200_CPB");
+    a.cpb_active = cpb_env ? (u32)std::atoi(cpb_env) : 4;
     int sms = 0;
     CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
-    static const bool use_v1 = std::getenv("CONCRETE_B200_W32_V1") != nullptr;
-    if (use_v1) {
+    static const char *ver_env = std::getenv("CONCRETE_B200_W32");
+    static const int ver = ver_env ? std::atoi(ver_env) : 3;
+    if (ver == 1) {
       CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)w32::SMEM_BYTES));
       const u32 ctas = (num_samples + w32::CPB - 1) / w32::CPB;
       const u32 grid = std::min<u32>((u32)sms, ctas);
       w32::pbs_kernel_w32<<<grid, w32::NTHREADS, w32::SMEM_BYTES, stream>>>(a);
-    } else {
+    } else if (ver == 2) {
       CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32v2,
                                     cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)w32::SMEM_BYTES2));
-      const u32 ctas = (num_samples + w32::CPB2 - 1) / w32::CPB2;
+      const u32 ctas = (num_samples + a.cpb_active - 1) / a.cpb_active;
       const u32 grid = std::min<u32>((u32)sms, ctas);
       w32::pbs_kernel_w32v2<<<grid, w32::NTHREADS2, w32::SMEM_BYTES2, stream>>>(a);
+    } else {
+      auto kern = w32::pbs_kernel_w32v3;
+      CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)w32::SMEM_BYTES3));
+      const u32 ctas = (num_samples + w32::CPB3 - 1) / w32::CPB3;
+      const u32 grid = std::min<u32>((u32)sms, ctas);
+      kern<<<grid, w32::NTHREADS3, w32::SMEM_BYTES3, stream>>>(a);
     }
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
@@ -533,6 +548,7 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   a.num_samples = num_samples;
   a.lut_count = lut_count;
   a.lut_stride = lut_stride;
+  a.skew_ns = 0;
   const size_t smem = pbs_smem_bytes(v, n);
   CB_CHECK(cudaFuncSetAttribute(v.pbs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   v.pbs<<<grid, v.T, smem, stream>>>(a);

@@ -166,7 +166,7 @@ __device__ __forceinline__ int digit_l1(u32 hi, u32 base_log) {
 
 // ---- K3 fast path ------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NTHREADS, 1) pbs_kernel_w32(const PbsArgs a) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *tws = reinterpret_cast<double2 *>(smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int ct = warp >> 1, r = warp & 1;
@@ -303,7 +303,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) pbs_kernel_w32(const PbsArgs a) {
 __global__ void __launch_bounds__(128) bsk_convert_kernel_w32(double2 *bsk,
                                                               const double2 *__restrict__ tw,
                                                               size_t num_polys) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *tws = reinterpret_cast<double2 *>(smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double2 *buf = reinterpret_cast<double2 *>(smem + SMEM_TW) + warp * M;
@@ -332,7 +332,7 @@ __global__ void __launch_bounds__(128) poly_mul_kernel_w32(const double *in1, co
                                                            double *out,
                                                            const double2 *__restrict__ tw,
                                                            u32 total) {
-  extern __shared__ __align__(16) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *tws = reinterpret_cast<double2 *>(smem);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   double2 *buf = reinterpret_cast<double2 *>(smem + SMEM_TW) + warp * M;

@@ -122,7 +122,7 @@ __device__ __forceinline__ void release_stage(V2Ctrl *ctrl, unsigned char *stage
 }
 
 __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a) {
-  extern __shared__ __align__(128) unsigned char smem[];
+  extern __shared__ __align__(1024) unsigned char smem[];
   double2 *tws = reinterpret_cast<double2 *>(smem);
   unsigned char *stage = smem + V2_OFF_STAGE;
   V2Ctrl *ctrl = reinterpret_cast<V2Ctrl *>(smem + V2_OFF_CTRL);
@@ -154,10 +154,13 @@ __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const u32 tmem_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) + (u32)(warp >> 2) * 128;
 
-  const u32 round_stride = gridDim.x * CPB2;
-  const u32 first = blockIdx.x * CPB2;
+  const u32 CPBA = a.cpb_active;
+  const u32 round_stride = gridDim.x * CPBA;
+  const u32 first = blockIdx.x * CPBA;
   if (tid == 0 && first < a.num_samples) issue_stage(stage, a.bsk, 0, &ctrl->full_bar);
   u32 full_parity = 0;
+  // de-phase the ciphertexts of the CTA so that their shared-memory and FP64 phases interleave
+  for (int d = 0; d < ct; ++d) __nanosleep(a.skew_ns);
 
   const double2 *g_own = reinterpret_cast<const double2 *>(stage) + (size_t)(r * 2 + r) * M + lane;
   const double2 *g_oth =
@@ -165,8 +168,8 @@ __global__ void __launch_bounds__(NTHREADS2, 1) pbs_kernel_w32v2(const PbsArgs a
 
   for (u32 base_s = first; base_s < a.num_samples; base_s += round_stride) {
     const u32 sample = base_s + ct;
-    if (sample >= a.num_samples) break; // higher ct slots stay inactive for good
-    const u32 n_active = min((u32)CPB2, a.num_samples - base_s);
+    if (sample >= a.num_samples || (u32)ct >= CPBA) break; // higher ct slots stay inactive for good
+    const u32 n_active = min(CPBA, a.num_samples - base_s);
     const bool more_rounds = (base_s + round_stride) < a.num_samples;
 
     const u64 *lwe = a.lwe_in + a.in_idx[sample] * (u64)(n + 1);

@@ -1,0 +1,590 @@
+// pbs_w32_v3.cuh — third generation of the warp-per-polynomial PBS kernel (N=2048, k=1, l=1).
+//
+// ncu on v2 with ONE ciphertext per CTA (profiles/r1_w32_v2_cpb1_*): a lone warp pair needs
+// 21 000 cycles per CMUX, four ciphertexts per SM need 26 500: v2 is bound by per-warp latency
+// (two warps per SM sub-partition cannot cover the LDS/DFMA/ALU dependency chains), not by a
+// pipe (FP64 45 %, shared-memory data pipe 49 %, issue slots 44 %).  v3 changes the occupancy
+// plan:
+//   * 6 ciphertexts = 12 warps per CTA, THREE warps per sub-partition, <= 168 registers: the
+//     thread's own accumulator pairs are no longer carried in registers between CMUXes but
+//     re-read from TMEM in 4-pair chunks, and the CMUX body is an out-of-line function so the
+//     caller's loop state is not live across the transforms;
+//   * shared memory = 12 x 16 KiB accumulator/transpose buffers + a 4 x 8 KiB key ring; the
+//     lane-dependent second-pass twiddles live in TMEM (tw[2^s + b + 1] = i * tw[2^s + b] for
+//     even b halves them; 80 columns per lane quadrant);
+//   * all 12 warps walk the CMUX index in lock-step and share every key fill: GGSW i streams
+//     through the ring in eight 8 KiB groups of 4 Fourier rows.  Slot and mbarrier parity of a
+//     group are compile-time constants (8 groups per CMUX, 4 slots); consumers wait on full[slot]
+//     and arrive on empty[slot]; one elected lane of warp 0 refills a slot three groups ahead
+//     (TMA bulk copies, complete_tx on full[slot]);
+//   * the last two forward stages, the product and the cross-term store are fused per group of
+//     4 rows (and the cross-term add with the first two inverse stages), so the
+//     shared-memory-bound product phase carries FP64 work instead of following it.
+// Measured alternative (kept out): de-phasing groups of warps so that FP64-bound and
+// shared-memory-bound phases of different ciphertexts overlap.  The unrolled CMUX body is
+// ~100 KB of SASS; three different instruction streams per sub-partition turn the kernel
+// instruction-fetch bound (stall_no_instruction 60-80 %, 1.6 IPC per SM, 20 % SLOWER than
+// lock-step where the 3 warps of a sub-partition share the fetch).
+// Arithmetic is unchanged from v1/v2 (same transforms, same rounding, same digit extraction).
+#pragma once
+
+namespace w32 {
+
+constexpr int CPB3 = 6;                 // ciphertexts per CTA
+constexpr int NW3 = 2 * CPB3;           // warps per CTA
+constexpr int NTHREADS3 = 32 * NW3;     // 384
+constexpr u32 V3_BUF_BYTES = (u32)M * 16;                       // 16 KiB per warp
+constexpr u32 V3_OFF_RING = (u32)NW3 * V3_BUF_BYTES;            // 196 608
+constexpr int V3_SLOTS = 4;
+constexpr u32 V3_SLOT_BYTES = 8192;     // 4 Fourier rows (p = 4g..4g+3) of the 4 GGSW polynomials
+constexpr int V3_GROUPS = 8;            // groups of 4 rows per GGSW
+constexpr u32 V3_OFF_CTRL = V3_OFF_RING + V3_SLOTS * V3_SLOT_BYTES;
+constexpr size_t SMEM_BYTES3 = V3_OFF_CTRL + 128;
+constexpr u32 V3_TMEM_COLS = 512;
+constexpr u32 V3_TW_COL = 384;          // twiddle columns of a lane quadrant (after 3 x 128 own)
+
+struct V3Ctrl {
+  unsigned long long full_bar[V3_SLOTS];  // fill landed (1 arrival + tx bytes)
+  unsigned int done_cnt[V3_SLOTS];        // warps done with the slot's current fill
+  unsigned int tmem_base;
+  unsigned int n, base_log, total_fills;
+  const double2 *bsk;
+};
+
+__device__ __forceinline__ u32 v3_ctrl_addr() {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  return smem_u32(smem) + V3_OFF_CTRL;
+}
+__device__ __forceinline__ void mbar_wait_s(u32 bar_addr, u32 parity) {
+  u32 done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(bar_addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void mbar_arrive_s(u32 bar_addr) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar_addr) : "memory");
+}
+__device__ __forceinline__ double2 lds128(u32 addr) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts128(u32 addr, const double2 v) {
+  asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v.x), "d"(v.y) : "memory");
+}
+
+// Fill t = cmux * 8 + g: rows 4g..4g+3 of the four polynomials of GGSW i -> slot g & 3.
+// One thread.  The caller has waited for empty[slot] of the previous fill.
+__device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
+  const u32 slot = g & (V3_SLOTS - 1);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
+  mbar_expect_tx(&ctrl->full_bar[slot], V3_SLOT_BYTES);
+  const double2 *src = ctrl->bsk + (size_t)i * 4 * M + (size_t)g * 4 * 32;
+  unsigned char *dst = smem + V3_OFF_RING + slot * V3_SLOT_BYTES;
+#pragma unroll
+  for (int poly = 0; poly < 4; ++poly)
+    tma_load_bulk(dst + poly * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot]);
+}
+
+// consumer side of group G: the fill of rows 4G..4G+3 (slot and parity are static).
+// try_once issues one non-looping try_wait whose ~90-cycle latency can be covered by other work.
+template <int G> __device__ __forceinline__ u32 v3_try_full() {
+  u32 done;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(done)
+      : "r"(v3_ctrl_addr() + 8 * (G & (V3_SLOTS - 1))), "n"((G >> 2) & 1)
+      : "memory");
+  return done;
+}
+template <int G> __device__ __forceinline__ void v3_wait_full(u32 tried) {
+  if (!tried) mbar_wait_s(v3_ctrl_addr() + 8 * (G & (V3_SLOTS - 1)), (G >> 2) & 1);
+}
+// This warp has issued its last read of fill t0 + G: count it (shared-memory operations of a
+// warp execute in order, so the count follows the reads).  Returns the previous count to lane 0.
+template <int G> __device__ __forceinline__ u32 v3_count_done(int lane) {
+  u32 old = 0;
+  __syncwarp();
+  if (lane == 0)
+    asm volatile("atom.shared.add.u32 %0, [%1], 1;"
+                 : "=r"(old)
+                 : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * (G & (V3_SLOTS - 1)))
+                 : "memory");
+  return old;
+}
+// The warp that counted last (all 12 done) refills the slot with the group 4 ahead.
+template <int G> __device__ __forceinline__ void v3_refill(u32 old, int lane, u32 t0, u32 i) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  if (lane == 0 && old == NW3 - 1) {
+    V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
+    ctrl->done_cnt[G & (V3_SLOTS - 1)] = 0;
+    if (t0 + G + V3_SLOTS < ctrl->total_fills) {
+      const u32 n = ctrl->n;
+      const u32 inext = (i + 1 == n) ? 0 : i + 1;
+      v3_issue_fill((G + V3_SLOTS >= V3_GROUPS) ? inext : i, (G + V3_SLOTS) & (V3_GROUPS - 1));
+    }
+  }
+}
+
+// a CMUX that adds nothing (a_hat == 0) or an idle ciphertext slot: only walk the ring
+template <int G> __device__ __forceinline__ void v3_idle_groups(u32 t0, u32 i, int lane) {
+  v3_wait_full<G>(0);
+  v3_refill<G>(v3_count_done<G>(lane), lane, t0, i);
+  if constexpr (G + 1 < V3_GROUPS) v3_idle_groups<G + 1>(t0, i, lane);
+}
+
+__device__ __forceinline__ void tmem_ld8(u32 taddr, u32 (&v)[8]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7])
+      : "r"(taddr)
+      : "memory");
+}
+
+__device__ __forceinline__ double2 mul_i(const double2 w) { return make_double2(-w.y, w.x); }
+template <int NV> __device__ __forceinline__ double2 tw_from(const u32 (&v)[NV], int e) {
+  return make_double2(__hiloint2double((int)v[4 * e + 1], (int)v[4 * e + 0]),
+                      __hiloint2double((int)v[4 * e + 3], (int)v[4 * e + 2]));
+}
+__device__ __forceinline__ double2 cmul(const double2 a, const double2 b) {
+  return make_double2(fma(a.x, b.x, -a.y * b.y), fma(a.x, b.y, a.y * b.x));
+}
+
+// Second-pass twiddles of this lane in TMEM (tw(s2,u) = tw[2^(s2+5) + (lane << s2) + u];
+// odd u = i * (u - 1)):
+//   columns  0..15 : (0,0) (1,0) (2,0) (2,2)
+//   columns 16+8g..: (4,2g) (3, g & ~1)            g = 0..7 (the group of rows 4g..4g+3)
+constexpr u32 V3_TW_NCOLS = 16 + 8 * V3_GROUPS;
+
+// stages s2 = 0,1,2 (forward) on all 32 points
+__device__ __forceinline__ void v3_fwd_stages012(double2 (&x)[32], const u32 (&v)[16]) {
+  const double2 t0 = tw_from<16>(v, 0), t1 = tw_from<16>(v, 1), t2a = tw_from<16>(v, 2),
+                t2b = tw_from<16>(v, 3);
+#pragma unroll
+  for (int lo = 0; lo < 16; ++lo) cbfft::bfly_ct(x[lo], x[lo | 16], t0);
+#pragma unroll
+  for (int u = 0; u < 2; ++u)
+#pragma unroll
+    for (int lo = 0; lo < 8; ++lo)
+      cbfft::bfly_ct(x[(u << 4) | lo], x[(u << 4) | lo | 8], u ? mul_i(t1) : t1);
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const double2 b = (u & 2) ? t2b : t2a;
+#pragma unroll
+    for (int lo = 0; lo < 4; ++lo)
+      cbfft::bfly_ct(x[(u << 3) | lo], x[(u << 3) | lo | 4], (u & 1) ? mul_i(b) : b);
+  }
+}
+__device__ __forceinline__ void v3_inv_stages210(double2 (&x)[32], const u32 (&v)[16]) {
+  const double2 t0 = tw_from<16>(v, 0), t1 = tw_from<16>(v, 1), t2a = tw_from<16>(v, 2),
+                t2b = tw_from<16>(v, 3);
+#pragma unroll
+  for (int u = 0; u < 4; ++u) {
+    const double2 b = (u & 2) ? t2b : t2a;
+#pragma unroll
+    for (int lo = 0; lo < 4; ++lo)
+      cbfft::bfly_gs(x[(u << 3) | lo], x[(u << 3) | lo | 4], (u & 1) ? mul_i(b) : b);
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u)
+#pragma unroll
+    for (int lo = 0; lo < 8; ++lo)
+      cbfft::bfly_gs(x[(u << 4) | lo], x[(u << 4) | lo | 8], u ? mul_i(t1) : t1);
+#pragma unroll
+  for (int lo = 0; lo < 16; ++lo) cbfft::bfly_gs(x[lo], x[lo | 16], t0);
+}
+
+__device__ __forceinline__ void pack_pairs(u32 (&v)[16], const u64 (&re)[4], const u64 (&im)[4]) {
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    v[4 * e + 0] = (u32)re[e];
+    v[4 * e + 1] = (u32)(re[e] >> 32);
+    v[4 * e + 2] = (u32)im[e];
+    v[4 * e + 3] = (u32)(im[e] >> 32);
+  }
+}
+
+// closest_representable + balanced digit of a one-level decomposition from the high word:
+// floor((hi + 2^(k-1)) / 2^k) taken as a signed b-bit value, except that the reference maps
+// B/2 to +B/2 (decomposer.rs:23-47, iter.rs:121-133 with state >> base_log == 0).  k = 32 - b.
+__device__ __forceinline__ int digit_l1_k(u32 hi, u32 kshift) {
+  const int sv = (int)(hi + (1u << (kshift - 1))) >> kshift;
+  const int half = 1 << (31 - kshift);
+  return (sv == -half) ? half : sv;
+}
+__device__ __forceinline__ ulonglong2 lds_u64x2(u32 addr) {
+  ulonglong2 v;
+  asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr));
+  return v;
+}
+// digits of rows 4c..4c+3 (own pairs in v) into x
+template <int DUMMY>
+__device__ __forceinline__ void v3_digits(double2 (&x)[32], const u32 (&v)[16], int c, u32 s16,
+                                          u32 buf_s, u32 kshift) {
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int p = 4 * c + e;
+    const u64 own_re = ((u64)v[4 * e + 1] << 32) | v[4 * e + 0];
+    const u64 own_im = ((u64)v[4 * e + 3] << 32) | v[4 * e + 2];
+    const u32 sp = s16 + 512u * p;
+    const ulonglong2 src = lds_u64x2(buf_s + (sp & 0x3FF0u));
+    const bool sw = (sp & 0x4000u) != 0, nre = (sp & 0x8000u) != 0, nim = sw != nre;
+    const u64 ra = sw ? src.y : src.x;
+    const u64 rb = sw ? src.x : src.y;
+    const u64 c_re = (nre ? (u64)0 - ra : ra) - own_re;
+    const u64 c_im = (nim ? (u64)0 - rb : rb) - own_im;
+    x[p].x = __int2double_rn(digit_l1_k((u32)(c_re >> 32), kshift));
+    x[p].y = __int2double_rn(digit_l1_k((u32)(c_im >> 32), kshift));
+  }
+}
+
+// Shared-memory addresses of this thread inside its warp's 16 KiB buffer (buffer base is
+// 1 KiB aligned, so the XOR swizzle folds into one LOP3 with an immediate):
+//   row layout   (index 32*lane + p, key lane): (rowb | 16p) ^ l7s
+//   column layout(index lane + 32p,  key p)   : (colb ^ 16(p & 7)) + 512p
+struct V3Addr {
+  u32 rowb, colb, l7s;
+};
+__device__ __forceinline__ u32 v3_row(const V3Addr &A, int p) { return (A.rowb | (16u * p)) ^ A.l7s; }
+__device__ __forceinline__ u32 v3_col(const V3Addr &A, int p) {
+  return (A.colb ^ (16u * (p & 7))) + 512u * p;
+}
+
+// forward group G: stages s2 = 3,4 on rows 4G..4G+3, product with the Fourier key (own term in
+// place, cross term to the partner warp through this warp's buffer).  Software pipelined across
+// groups: on entry tv holds the twiddles of G (tcgen05.ld in flight) and `tried` the result of
+// an early try_wait on the fill of G; the body issues both for G + 1 under its own arithmetic.
+template <int G>
+__device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], u32 (&tv)[8], u32 tried,
+                                             const V3Addr &A, u32 tmem_tw, u32 key_own,
+                                             u32 key_oth, u32 t0, u32 i, int lane) {
+  v3_wait_full<G>(tried);
+  constexpr u32 so = (G & (V3_SLOTS - 1)) * V3_SLOT_BYTES;
+  double2 wo = lds128(key_oth + so), w = lds128(key_own + so);
+  u32 tried_next = 0;
+  if constexpr (G + 1 < V3_GROUPS) tried_next = v3_try_full<G + 1>();
+  tmem_wait_ld();
+  {
+    const double2 t4 = tw_from<8>(tv, 0);
+    const double2 t3 = (G & 1) ? mul_i(tw_from<8>(tv, 1)) : tw_from<8>(tv, 1);
+    cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 2], t3);
+    cbfft::bfly_ct(x[4 * G + 1], x[4 * G + 3], t3);
+    cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 1], t4);
+    cbfft::bfly_ct(x[4 * G + 2], x[4 * G + 3], mul_i(t4));
+  }
+  if constexpr (G + 1 < V3_GROUPS) tmem_ld8(tmem_tw + 16 + 8 * (G + 1), tv);
+  u32 old = 0;
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const int p = 4 * G + e;
+    double2 wo_n = wo, w_n = w;
+    if (e < 3) {
+      wo_n = lds128(key_oth + so + 512 * (e + 1));
+      w_n = lds128(key_own + so + 512 * (e + 1));
+    } else {
+      old = v3_count_done<G>(lane); // every read of the slot has been issued
+    }
+    sts128(v3_row(A, p), cmul(x[p], wo));
+    x[p] = cmul(x[p], w);
+    wo = wo_n;
+    w = w_n;
+  }
+  v3_refill<G>(old, lane, t0, i);
+  if constexpr (G + 1 < V3_GROUPS)
+    v3_fwd_group<G + 1>(x, tv, tried_next, A, tmem_tw, key_own, key_oth, t0, i, lane);
+}
+
+// inverse group G: add the partner's cross term, inverse stages s2 = 4,3
+template <int G>
+__device__ __forceinline__ void v3_inv_group(double2 (&x)[32], const V3Addr &A, u32 tmem_tw,
+                                             u32 oth_delta) {
+  u32 tv[8];
+  tmem_ld8(tmem_tw + 16 + 8 * G, tv);
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    double2 o[2];
+#pragma unroll
+    for (int e = 0; e < 2; ++e) o[e] = lds128(v3_row(A, 4 * G + 2 * h + e) + oth_delta);
+#pragma unroll
+    for (int e = 0; e < 2; ++e) {
+      x[4 * G + 2 * h + e].x += o[e].x;
+      x[4 * G + 2 * h + e].y += o[e].y;
+    }
+  }
+  tmem_wait_ld();
+  const double2 t4 = tw_from<8>(tv, 0);
+  const double2 t3 = (G & 1) ? mul_i(tw_from<8>(tv, 1)) : tw_from<8>(tv, 1);
+  cbfft::bfly_gs(x[4 * G + 0], x[4 * G + 1], t4);
+  cbfft::bfly_gs(x[4 * G + 2], x[4 * G + 3], mul_i(t4));
+  cbfft::bfly_gs(x[4 * G + 0], x[4 * G + 2], t3);
+  cbfft::bfly_gs(x[4 * G + 1], x[4 * G + 3], t3);
+  if constexpr (G + 1 < V3_GROUPS) v3_inv_group<G + 1>(x, A, tmem_tw, oth_delta);
+}
+
+// One CMUX of one polynomial (one warp).  Kept out of line on purpose: with 128 of the 168
+// registers holding the 32 complex points, the loop state of the caller (round, sample, LWE
+// pointer, counters) must not stay live across the transforms; everything the body needs beyond
+// its three arguments is re-derived from the thread index or read from the control block.
+__device__ __noinline__ void v3_cmux(const u32 a_hat, const u32 t0, const u32 i) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = warp & 1;
+  V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
+  const u32 buf_s = smem_u32(smem) + (u32)warp * V3_BUF_BYTES;
+  V3Addr A;
+  A.rowb = buf_s + 512u * lane;
+  A.colb = buf_s + 16u * lane;
+  A.l7s = (lane & 7) << 4;
+  const u32 tmem_quad = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16);
+  const u32 tmem_own = tmem_quad + (u32)(warp >> 2) * 128; // a third of the quadrant's columns
+  const u32 tmem_tw = tmem_quad + V3_TW_COL;
+
+  double2 x[32];
+  { // ct1 = ACC*X^a - ACC, closest_representable, signed digit (l = 1) -> doubles
+    const u32 kshift = 32 - ctrl->base_log;
+    // 16 * ((lane - a_hat) mod 4096): bits 4..13 address the pair, bit 14 swaps (re, im), bit 15
+    // negates re, bit 14 ^ bit 15 negates im  (multiplication by (-i)^q, q = bits 15:14)
+    const u32 s16 = ((u32)(lane - (int)a_hat) << 4) & 0xFFF0u;
+    u32 va[16], vb[16];
+    tmem_ld16(tmem_own, va);
+    tmem_wait_ld();
+#pragma unroll
+    for (int cc = 0; cc < 4; ++cc) {
+      tmem_ld16(tmem_own + 16 * (2 * cc + 1), vb);
+      v3_digits<0>(x, va, 2 * cc, s16, buf_s, kshift);
+      tmem_wait_ld();
+      if (cc < 3) tmem_ld16(tmem_own + 16 * (2 * cc + 2), va);
+      v3_digits<0>(x, vb, 2 * cc + 1, s16, buf_s, kshift);
+      if (cc < 3) tmem_wait_ld();
+    }
+  }
+
+  fwd_pass1(x);
+  __syncwarp(); // rotated reads of the accumulator are done in every lane
+#pragma unroll
+  for (int p = 0; p < 32; ++p) sts128(v3_col(A, p), x[p]);
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) x[p] = lds128(v3_row(A, p));
+  {
+    u32 v[16];
+    tmem_ld16(tmem_tw, v);
+    tmem_wait_ld();
+    v3_fwd_stages012(x, v);
+  }
+
+  __syncwarp(); // transpose reads of the buffer are done in every lane
+  {
+    const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * lane;
+    u32 tv[8];
+    tmem_ld8(tmem_tw + 16, tv);
+    v3_fwd_group<0>(x, tv, 0, A, tmem_tw, key + (r * 2 + r) * 2048,
+                    key + (r * 2 + (1 - r)) * 2048, t0, i, lane);
+  }
+
+  asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp >> 1)) : "memory");
+  v3_inv_group<0>(x, A, tmem_tw, r ? 0u - V3_BUF_BYTES : V3_BUF_BYTES);
+  asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp >> 1)) : "memory"); // partner done with buf
+  {
+    u32 v[16];
+    tmem_ld16(tmem_tw, v);
+    tmem_wait_ld();
+    v3_inv_stages210(x, v);
+  }
+#pragma unroll
+  for (int p = 0; p < 32; ++p) sts128(v3_row(A, p), x[p]);
+  __syncwarp();
+#pragma unroll
+  for (int p = 0; p < 32; ++p) x[p] = lds128(v3_col(A, p));
+  inv_pass1(x);
+
+  // ACC += round(x): own copy from TMEM; the new value goes back to TMEM and to the shared
+  // home for the rotated read of the next CMUX
+  __syncwarp(); // transpose reads of the buffer are done before it becomes the accumulator again
+  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)warp * V3_BUF_BYTES);
+#pragma unroll
+  for (int c = 0; c < 8; ++c) {
+    u32 v[16];
+    tmem_ld16(tmem_own + 16 * c, v);
+    tmem_wait_ld();
+    u64 re[4], im[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int p = 4 * c + e;
+      re[e] = (((u64)v[4 * e + 1] << 32) | v[4 * e + 0]) + from_torus_scaled(x[p].x);
+      im[e] = (((u64)v[4 * e + 3] << 32) | v[4 * e + 2]) + from_torus_scaled(x[p].y);
+      acc[lane + 32 * p] = make_ulonglong2(re[e], im[e]);
+    }
+    pack_pairs(v, re, im);
+    tmem_st16(tmem_own + 16 * c, v);
+  }
+  tmem_wait_st();
+  __syncwarp();
+}
+
+__global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int ct = warp >> 1, r = warp & 1;
+  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)warp * V3_BUF_BYTES);
+  V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
+  const u32 n = a.n;
+  const size_t out_size = (size_t)N + 1;
+
+  const u32 round_stride = gridDim.x * CPB3;
+  const u32 first = blockIdx.x * CPB3;
+  const u32 rounds =
+      (first < a.num_samples) ? (a.num_samples - first + round_stride - 1) / round_stride : 0;
+  const u32 total_fills = rounds * n * V3_GROUPS;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < V3_SLOTS; ++s) {
+      mbar_init(&ctrl->full_bar[s], 1);
+      ctrl->done_cnt[s] = 0;
+    }
+    ctrl->n = n;
+    ctrl->base_log = a.base_log;
+    ctrl->total_fills = total_fills;
+    ctrl->bsk = a.bsk;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(&ctrl->tmem_base)),
+                 "r"(V3_TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const u32 tmem_quad = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16);
+  const u32 tmem_own = tmem_quad + (u32)(warp >> 2) * 128;
+  const u32 tmem_tw = tmem_quad + V3_TW_COL;
+
+  if (warp < 4) { // one warp per lane quadrant stores the quadrant's twiddle columns
+#pragma unroll
+    for (int c = 0; c < (int)V3_TW_NCOLS / 16; ++c) {
+      u32 v[16];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int idx = 4 * c + e; // twiddle slot (4 columns each)
+        int s2, u;
+        if (idx < 2) { s2 = idx; u = 0; }
+        else if (idx < 4) { s2 = 2; u = 2 * (idx - 2); }
+        else {
+          const int g = (idx - 4) >> 1;
+          if ((idx & 1) == 0) { s2 = 4; u = 2 * g; }
+          else { s2 = 3; u = g & ~1; }
+        }
+        const double2 w = a.tw[(1 << (s2 + 5)) + (lane << s2) + u];
+        v[4 * e + 0] = (u32)__double2loint(w.x);
+        v[4 * e + 1] = (u32)__double2hiint(w.x);
+        v[4 * e + 2] = (u32)__double2loint(w.y);
+        v[4 * e + 3] = (u32)__double2hiint(w.y);
+      }
+      tmem_st16(tmem_tw + 16 * c, v);
+    }
+    tmem_wait_st();
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+
+  if (tid == 0) { // prologue: groups 0..3 of the first GGSW fill the four slots
+    for (u32 g = 0; g < (u32)V3_SLOTS && g < total_fills; ++g) v3_issue_fill(0, g);
+  }
+
+  u32 cmux = 0; // CMUX rounds of this CTA so far (every warp sees every one of them)
+  for (u32 rd = 0; rd < rounds; ++rd) {
+    const u32 sample = first + rd * round_stride + ct;
+    const bool active = sample < a.num_samples;
+    const u64 *lwe = a.lwe_in + (active ? a.in_idx[sample] : 0) * (u64)(n + 1);
+
+    if (active) {
+      const u32 b_hat = modulus_switch(__ldg(&lwe[n]), LOGM + 2);
+      const u64 *lut = a.lut_vector + a.lut_idx[sample] * (u64)(2 * N) + (size_t)r * N;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        u64 re[4], im[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int j = lane + 32 * (4 * c + e);
+          {
+            const u32 u = (j + b_hat) & (2 * N - 1);
+            const u64 w = __ldg(&lut[u & (N - 1)]);
+            re[e] = (u < (u32)N) ? w : (u64)0 - w;
+          }
+          {
+            const u32 u = (j + M + b_hat) & (2 * N - 1);
+            const u64 w = __ldg(&lut[u & (N - 1)]);
+            im[e] = (u < (u32)N) ? w : (u64)0 - w;
+          }
+          acc[j] = make_ulonglong2(re[e], im[e]);
+        }
+        u32 v[16];
+        pack_pairs(v, re, im);
+        tmem_st16(tmem_own + 16 * c, v);
+      }
+      tmem_wait_st();
+    }
+    __syncwarp();
+
+    u32 a_next = active ? modulus_switch(__ldg(&lwe[0]), LOGM + 2) : 0;
+#pragma unroll 1
+    for (u32 i = 0; i < n; ++i, ++cmux) {
+      const u32 a_hat = a_next;
+      if (active && i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), LOGM + 2);
+      const u32 t0 = cmux * V3_GROUPS;
+      if (a_hat == 0) // X^0 - 1 = 0: no CMUX (bootstrap.rs:287); still walk the ring
+        v3_idle_groups<0>(t0, i, lane);
+      else
+        v3_cmux(a_hat, t0, i);
+    }
+
+    // sample extraction: warp 0 of the pair holds the mask polynomial, warp 1 the body
+    if (active) {
+      for (u32 li = 0; li < a.lut_count; ++li) {
+        const u32 nth = li * a.lut_stride;
+        u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
+        if (r == 0) {
+          for (int xo = lane; xo < N; xo += 32) {
+            const int src = (xo <= (int)nth) ? ((int)nth - xo) : (N + (int)nth - xo);
+            const ulonglong2 pr = acc[src & (M - 1)];
+            const u64 v = (src < M) ? pr.x : pr.y;
+            out[xo] = (xo <= (int)nth) ? v : (u64)0 - v;
+          }
+        } else if (lane == 0) {
+          const ulonglong2 pr = acc[nth & (M - 1)];
+          out[N] = (nth < (u32)M) ? pr.x : pr.y;
+        }
+      }
+    }
+    __syncwarp();
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(ctrl->tmem_base),
+                 "r"(V3_TMEM_COLS)
+                 : "memory");
+}
+
+} // namespace w32
