@@ -39,7 +39,7 @@ constexpr int V3_SLOTS = 4;
 constexpr u32 V3_SLOT_BYTES = 8192;     // 4 Fourier rows (p = 4g..4g+3) of the 4 GGSW polynomials
 constexpr int V3_GROUPS = 8;            // groups of 4 rows per GGSW
 constexpr u32 V3_OFF_CTRL = V3_OFF_RING + V3_SLOTS * V3_SLOT_BYTES;
-constexpr size_t SMEM_BYTES3 = V3_OFF_CTRL + 128;
+constexpr size_t SMEM_BYTES3 = V3_OFF_CTRL + 256;
 constexpr u32 V3_TMEM_COLS = 512;
 constexpr u32 V3_TW_COL = 384;          // twiddle columns of a lane quadrant (after 3 x 128 own)
 
@@ -49,6 +49,7 @@ struct V3Ctrl {
   unsigned int tmem_base;
   unsigned int n, base_log, total_fills;
   const double2 *bsk;
+  unsigned int wt0[NW3], wi[NW3];         // per warp: fill index base and GGSW index of its CMUX
 };
 
 __device__ __forceinline__ u32 v3_ctrl_addr() {
@@ -91,9 +92,13 @@ __device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
   mbar_expect_tx(&ctrl->full_bar[slot], V3_SLOT_BYTES);
   const double2 *src = ctrl->bsk + (size_t)i * 4 * M + (size_t)g * 4 * 32;
   unsigned char *dst = smem + V3_OFF_RING + slot * V3_SLOT_BYTES;
+  // slot layout [r][own, cross]: polynomial (row r, column c) of the GGSW goes to position
+  // 2r + (c != r), so a warp addresses both of its polynomials from one base register
 #pragma unroll
-  for (int poly = 0; poly < 4; ++poly)
-    tma_load_bulk(dst + poly * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot]);
+  for (int poly = 0; poly < 4; ++poly) {
+    const int r = poly >> 1, c = poly & 1, pos = 2 * r + (c != r);
+    tma_load_bulk(dst + pos * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot]);
+  }
 }
 
 // consumer side of group G: the fill of rows 4G..4G+3 (slot and parity are static).
@@ -120,18 +125,18 @@ template <int G> __device__ __forceinline__ u32 v3_count_done(int lane) {
   u32 old = 0;
   __syncwarp();
   if (lane == 0)
-    asm volatile("atom.shared.add.u32 %0, [%1], 1;"
+    asm volatile("atom.shared.inc.u32 %0, [%1], %2;" // wraps to 0 after the 12th warp
                  : "=r"(old)
-                 : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * (G & (V3_SLOTS - 1)))
+                 : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * (G & (V3_SLOTS - 1))), "n"(NW3 - 1)
                  : "memory");
   return old;
 }
 // The warp that counted last (all 12 done) refills the slot with the group 4 ahead.
-template <int G> __device__ __forceinline__ void v3_refill(u32 old, int lane, u32 t0, u32 i) {
+template <int G> __device__ __forceinline__ void v3_refill(u32 old, int lane) {
   extern __shared__ __align__(1024) unsigned char smem[];
   if (lane == 0 && old == NW3 - 1) {
     V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
-    ctrl->done_cnt[G & (V3_SLOTS - 1)] = 0;
+    const u32 t0 = ctrl->wt0[threadIdx.x >> 5], i = ctrl->wi[threadIdx.x >> 5];
     if (t0 + G + V3_SLOTS < ctrl->total_fills) {
       const u32 n = ctrl->n;
       const u32 inext = (i + 1 == n) ? 0 : i + 1;
@@ -141,10 +146,10 @@ template <int G> __device__ __forceinline__ void v3_refill(u32 old, int lane, u3
 }
 
 // a CMUX that adds nothing (a_hat == 0) or an idle ciphertext slot: only walk the ring
-template <int G> __device__ __forceinline__ void v3_idle_groups(u32 t0, u32 i, int lane) {
+template <int G> __device__ __forceinline__ void v3_idle_groups(int lane) {
   v3_wait_full<G>(0);
-  v3_refill<G>(v3_count_done<G>(lane), lane, t0, i);
-  if constexpr (G + 1 < V3_GROUPS) v3_idle_groups<G + 1>(t0, i, lane);
+  v3_refill<G>(v3_count_done<G>(lane), lane);
+  if constexpr (G + 1 < V3_GROUPS) v3_idle_groups<G + 1>(lane);
 }
 
 __device__ __forceinline__ void tmem_ld8(u32 taddr, u32 (&v)[8]) {
@@ -154,6 +159,18 @@ __device__ __forceinline__ void tmem_ld8(u32 taddr, u32 (&v)[8]) {
         "=r"(v[7])
       : "r"(taddr)
       : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld4(u32 taddr, u32 (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr)
+               : "memory");
+}
+// one twiddle (4 columns): an x4 load needs only a 4-aligned register quad, like LDS.128; the
+// x8/x16 forms need 8/16 consecutive registers, which ptxas can only find by spilling points
+__device__ __forceinline__ double2 tw_of(const u32 (&v)[4]) {
+  return make_double2(__hiloint2double((int)v[1], (int)v[0]), __hiloint2double((int)v[3], (int)v[2]));
 }
 
 __device__ __forceinline__ double2 mul_i(const double2 w) { return make_double2(-w.y, w.x); }
@@ -172,9 +189,12 @@ __device__ __forceinline__ double2 cmul(const double2 a, const double2 b) {
 constexpr u32 V3_TW_NCOLS = 16 + 8 * V3_GROUPS;
 
 // stages s2 = 0,1,2 (forward) on all 32 points
-__device__ __forceinline__ void v3_fwd_stages012(double2 (&x)[32], const u32 (&v)[16]) {
-  const double2 t0 = tw_from<16>(v, 0), t1 = tw_from<16>(v, 1), t2a = tw_from<16>(v, 2),
-                t2b = tw_from<16>(v, 3);
+__device__ __forceinline__ void v3_fwd_stages012(double2 (&x)[32], u32 tmem_tw) {
+  u32 va[4], vb[4];
+  tmem_ld4(tmem_tw, va);
+  tmem_ld4(tmem_tw + 4, vb);
+  tmem_wait_ld();
+  const double2 t0 = tw_of(va), t1 = tw_of(vb);
 #pragma unroll
   for (int lo = 0; lo < 16; ++lo) cbfft::bfly_ct(x[lo], x[lo | 16], t0);
 #pragma unroll
@@ -182,6 +202,10 @@ __device__ __forceinline__ void v3_fwd_stages012(double2 (&x)[32], const u32 (&v
 #pragma unroll
     for (int lo = 0; lo < 8; ++lo)
       cbfft::bfly_ct(x[(u << 4) | lo], x[(u << 4) | lo | 8], u ? mul_i(t1) : t1);
+  tmem_ld4(tmem_tw + 8, va);
+  tmem_ld4(tmem_tw + 12, vb);
+  tmem_wait_ld();
+  const double2 t2a = tw_of(va), t2b = tw_of(vb);
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
     const double2 b = (u & 2) ? t2b : t2a;
@@ -190,9 +214,12 @@ __device__ __forceinline__ void v3_fwd_stages012(double2 (&x)[32], const u32 (&v
       cbfft::bfly_ct(x[(u << 3) | lo], x[(u << 3) | lo | 4], (u & 1) ? mul_i(b) : b);
   }
 }
-__device__ __forceinline__ void v3_inv_stages210(double2 (&x)[32], const u32 (&v)[16]) {
-  const double2 t0 = tw_from<16>(v, 0), t1 = tw_from<16>(v, 1), t2a = tw_from<16>(v, 2),
-                t2b = tw_from<16>(v, 3);
+__device__ __forceinline__ void v3_inv_stages210(double2 (&x)[32], u32 tmem_tw) {
+  u32 va[4], vb[4];
+  tmem_ld4(tmem_tw + 8, va);
+  tmem_ld4(tmem_tw + 12, vb);
+  tmem_wait_ld();
+  const double2 t2a = tw_of(va), t2b = tw_of(vb);
 #pragma unroll
   for (int u = 0; u < 4; ++u) {
     const double2 b = (u & 2) ? t2b : t2a;
@@ -200,6 +227,10 @@ __device__ __forceinline__ void v3_inv_stages210(double2 (&x)[32], const u32 (&v
     for (int lo = 0; lo < 4; ++lo)
       cbfft::bfly_gs(x[(u << 3) | lo], x[(u << 3) | lo | 4], (u & 1) ? mul_i(b) : b);
   }
+  tmem_ld4(tmem_tw, va);
+  tmem_ld4(tmem_tw + 4, vb);
+  tmem_wait_ld();
+  const double2 t0 = tw_of(va), t1 = tw_of(vb);
 #pragma unroll
   for (int u = 0; u < 2; ++u)
 #pragma unroll
@@ -253,16 +284,80 @@ __device__ __forceinline__ void v3_digits(double2 (&x)[32], const u32 (&v)[16], 
   }
 }
 
-// Shared-memory addresses of this thread inside its warp's 16 KiB buffer (buffer base is
-// 1 KiB aligned, so the XOR swizzle folds into one LOP3 with an immediate):
-//   row layout   (index 32*lane + p, key lane): (rowb | 16p) ^ l7s
+// Shared-memory addresses of this thread inside its warp's 16 KiB buffer (the buffer base is
+// 1 KiB aligned).  Each address is ONE just-in-time XOR with an immediate plus an immediate
+// offset in the load/store; the XOR is an opaque asm so that ptxas does not keep the eight
+// swizzle variants of both layouts live across the transforms (16 registers it does not have):
+//   row layout   (index 32*lane + p, key lane): (rowx ^ 16(p & 7)) + 128(p >> 3)
 //   column layout(index lane + 32p,  key p)   : (colb ^ 16(p & 7)) + 512p
+// with rowx = buf + 512*lane + 16*(lane & 7), colb = buf + 16*lane.
 struct V3Addr {
-  u32 rowb, colb, l7s;
+  u32 rowx, colb;
 };
-__device__ __forceinline__ u32 v3_row(const V3Addr &A, int p) { return (A.rowb | (16u * p)) ^ A.l7s; }
-__device__ __forceinline__ u32 v3_col(const V3Addr &A, int p) {
-  return (A.colb ^ (16u * (p & 7))) + 512u * p;
+template <u32 OFF> __device__ __forceinline__ double2 lds128o(u32 addr) {
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(v.x), "=d"(v.y) : "r"(addr), "n"(OFF));
+  return v;
+}
+// load / store at ((base ^ XORI) + OFF): the XOR lives inside the asm so that no address
+// register outlives the access
+template <u32 XORI, u32 OFF> __device__ __forceinline__ double2 lds128x(u32 base) {
+  double2 v;
+  asm volatile(
+      "{\n"
+      ".reg .b32 t;\n"
+      "xor.b32 t, %2, %3;\n"
+      "ld.shared.v2.f64 {%0, %1}, [t+%4];\n"
+      "}\n"
+      : "=d"(v.x), "=d"(v.y)
+      : "r"(base), "n"(XORI), "n"(OFF));
+  return v;
+}
+template <u32 XORI, u32 OFF> __device__ __forceinline__ void sts128x(u32 base, const double2 v) {
+  asm volatile(
+      "{\n"
+      ".reg .b32 t;\n"
+      "xor.b32 t, %0, %1;\n"
+      "st.shared.v2.f64 [t+%2], {%3, %4};\n"
+      "}\n" ::"r"(base),
+      "n"(XORI), "n"(OFF), "d"(v.x), "d"(v.y)
+      : "memory");
+}
+template <int P> __device__ __forceinline__ double2 ld_row(const V3Addr &A, u32 delta = 0) {
+  return lds128x<16u * (P & 7), 128u * (P >> 3)>(A.rowx + delta);
+}
+template <int P> __device__ __forceinline__ void st_row(const V3Addr &A, const double2 v) {
+  sts128x<16u * (P & 7), 128u * (P >> 3)>(A.rowx, v);
+}
+template <int P> __device__ __forceinline__ double2 ld_col(const V3Addr &A) {
+  return lds128x<16u * (P & 7), 512u * P>(A.colb);
+}
+template <int P> __device__ __forceinline__ void st_col(const V3Addr &A, const double2 v) {
+  sts128x<16u * (P & 7), 512u * P>(A.colb, v);
+}
+template <int P> __device__ __forceinline__ void st_col_all(const V3Addr &A, const double2 (&x)[32]) {
+  st_col<P>(A, x[P]);
+  if constexpr (P + 1 < 32) st_col_all<P + 1>(A, x);
+}
+template <int P> __device__ __forceinline__ void ld_col_all(const V3Addr &A, double2 (&x)[32]) {
+  x[P] = ld_col<P>(A);
+  if constexpr (P + 1 < 32) ld_col_all<P + 1>(A, x);
+}
+template <int P> __device__ __forceinline__ void st_row_all(const V3Addr &A, const double2 (&x)[32]) {
+  st_row<P>(A, x[P]);
+  if constexpr (P + 1 < 32) st_row_all<P + 1>(A, x);
+}
+template <int P> __device__ __forceinline__ void ld_row_all(const V3Addr &A, double2 (&x)[32]) {
+  x[P] = ld_row<P>(A);
+  if constexpr (P + 1 < 32) ld_row_all<P + 1>(A, x);
+}
+
+// product of row P with the staged key: cross term to the partner through buf, own term in place
+template <int P, u32 SO>
+__device__ __forceinline__ void v3_product(double2 (&x)[32], const V3Addr &A, u32 keyr) {
+  const double2 w = lds128o<SO + 512 * (P & 3)>(keyr), wo = lds128o<SO + 2048 + 512 * (P & 3)>(keyr);
+  st_row<P>(A, cmul(x[P], wo));
+  x[P] = cmul(x[P], w);
 }
 
 // forward group G: stages s2 = 3,4 on rows 4G..4G+3, product with the Fourier key (own term in
@@ -270,65 +365,59 @@ __device__ __forceinline__ u32 v3_col(const V3Addr &A, int p) {
 // groups: on entry tv holds the twiddles of G (tcgen05.ld in flight) and `tried` the result of
 // an early try_wait on the fill of G; the body issues both for G + 1 under its own arithmetic.
 template <int G>
-__device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], u32 (&tv)[8], u32 tried,
-                                             const V3Addr &A, u32 tmem_tw, u32 key_own,
-                                             u32 key_oth, u32 t0, u32 i, int lane) {
-  v3_wait_full<G>(tried);
-  constexpr u32 so = (G & (V3_SLOTS - 1)) * V3_SLOT_BYTES;
-  double2 wo = lds128(key_oth + so), w = lds128(key_own + so);
-  u32 tried_next = 0;
-  if constexpr (G + 1 < V3_GROUPS) tried_next = v3_try_full<G + 1>();
-  tmem_wait_ld();
+__device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], const V3Addr &A, u32 tmem_tw,
+                                             u32 keyr, int lane) {
   {
-    const double2 t4 = tw_from<8>(tv, 0);
-    const double2 t3 = (G & 1) ? mul_i(tw_from<8>(tv, 1)) : tw_from<8>(tv, 1);
+    u32 ta[4], tb[4];
+    tmem_ld4(tmem_tw + 16 + 8 * G, ta);
+    tmem_ld4(tmem_tw + 20 + 8 * G, tb);
+    tmem_wait_ld();
+    const double2 t4 = tw_of(ta);
+    const double2 t3 = (G & 1) ? mul_i(tw_of(tb)) : tw_of(tb);
     cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 2], t3);
     cbfft::bfly_ct(x[4 * G + 1], x[4 * G + 3], t3);
     cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 1], t4);
     cbfft::bfly_ct(x[4 * G + 2], x[4 * G + 3], mul_i(t4));
   }
-  if constexpr (G + 1 < V3_GROUPS) tmem_ld8(tmem_tw + 16 + 8 * (G + 1), tv);
+  v3_wait_full<G>(0);
+  constexpr u32 so = (G & (V3_SLOTS - 1)) * V3_SLOT_BYTES;
   u32 old = 0;
-#pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const int p = 4 * G + e;
-    double2 wo_n = wo, w_n = w;
-    if (e < 3) {
-      wo_n = lds128(key_oth + so + 512 * (e + 1));
-      w_n = lds128(key_own + so + 512 * (e + 1));
-    } else {
-      old = v3_count_done<G>(lane); // every read of the slot has been issued
-    }
-    sts128(v3_row(A, p), cmul(x[p], wo));
+  v3_product<4 * G + 0, so>(x, A, keyr);
+  v3_product<4 * G + 1, so>(x, A, keyr);
+  v3_product<4 * G + 2, so>(x, A, keyr);
+  {
+    constexpr int p = 4 * G + 3;
+    const double2 w = lds128o<so + 512 * 3>(keyr), wo = lds128o<so + 2048 + 512 * 3>(keyr);
+    old = v3_count_done<G>(lane); // every read of the slot has been issued
+    st_row<p>(A, cmul(x[p], wo));
     x[p] = cmul(x[p], w);
-    wo = wo_n;
-    w = w_n;
   }
-  v3_refill<G>(old, lane, t0, i);
-  if constexpr (G + 1 < V3_GROUPS)
-    v3_fwd_group<G + 1>(x, tv, tried_next, A, tmem_tw, key_own, key_oth, t0, i, lane);
+  v3_refill<G>(old, lane);
+  if constexpr (G + 1 < V3_GROUPS) v3_fwd_group<G + 1>(x, A, tmem_tw, keyr, lane);
 }
 
 // inverse group G: add the partner's cross term, inverse stages s2 = 4,3
 template <int G>
 __device__ __forceinline__ void v3_inv_group(double2 (&x)[32], const V3Addr &A, u32 tmem_tw,
                                              u32 oth_delta) {
-  u32 tv[8];
-  tmem_ld8(tmem_tw + 16 + 8 * G, tv);
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    double2 o[2];
-#pragma unroll
-    for (int e = 0; e < 2; ++e) o[e] = lds128(v3_row(A, 4 * G + 2 * h + e) + oth_delta);
-#pragma unroll
-    for (int e = 0; e < 2; ++e) {
-      x[4 * G + 2 * h + e].x += o[e].x;
-      x[4 * G + 2 * h + e].y += o[e].y;
-    }
+  u32 ta[4], tb[4];
+  tmem_ld4(tmem_tw + 16 + 8 * G, ta);
+  tmem_ld4(tmem_tw + 20 + 8 * G, tb);
+  {
+    const double2 o0 = ld_row<4 * G + 0>(A, oth_delta), o1 = ld_row<4 * G + 1>(A, oth_delta);
+    x[4 * G + 0].x += o0.x;
+    x[4 * G + 0].y += o0.y;
+    x[4 * G + 1].x += o1.x;
+    x[4 * G + 1].y += o1.y;
+    const double2 o2 = ld_row<4 * G + 2>(A, oth_delta), o3 = ld_row<4 * G + 3>(A, oth_delta);
+    x[4 * G + 2].x += o2.x;
+    x[4 * G + 2].y += o2.y;
+    x[4 * G + 3].x += o3.x;
+    x[4 * G + 3].y += o3.y;
   }
   tmem_wait_ld();
-  const double2 t4 = tw_from<8>(tv, 0);
-  const double2 t3 = (G & 1) ? mul_i(tw_from<8>(tv, 1)) : tw_from<8>(tv, 1);
+  const double2 t4 = tw_of(ta);
+  const double2 t3 = (G & 1) ? mul_i(tw_of(tb)) : tw_of(tb);
   cbfft::bfly_gs(x[4 * G + 0], x[4 * G + 1], t4);
   cbfft::bfly_gs(x[4 * G + 2], x[4 * G + 3], mul_i(t4));
   cbfft::bfly_gs(x[4 * G + 0], x[4 * G + 2], t3);
@@ -336,83 +425,96 @@ __device__ __forceinline__ void v3_inv_group(double2 (&x)[32], const V3Addr &A, 
   if constexpr (G + 1 < V3_GROUPS) v3_inv_group<G + 1>(x, A, tmem_tw, oth_delta);
 }
 
+// Per-phase thread state, rebuilt from a fresh (opaque) read of %tid.x: the values are cheap,
+// and separate live ranges keep ptxas from spilling one long-lived address register and
+// reloading it from local memory (L2 latency) in front of every shared-memory access.
+struct V3Phase {
+  int lane, warp;
+  u32 buf_s;
+  V3Addr A;
+  u32 tmem_own, tmem_tw;
+};
+__device__ __forceinline__ V3Phase v3_phase() {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  u32 tid;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+  V3Phase P;
+  P.lane = tid & 31;
+  P.warp = tid >> 5;
+  P.buf_s = smem_u32(smem) + (u32)P.warp * V3_BUF_BYTES;
+  P.A.rowx = P.buf_s + 512u * P.lane + 16u * (P.lane & 7);
+  P.A.colb = P.buf_s + 16u * P.lane;
+  u32 tb;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tb) : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * V3_SLOTS));
+  const u32 tmem_quad = tb + ((u32)((P.warp & 3) * 32) << 16);
+  P.tmem_own = tmem_quad + (u32)(P.warp >> 2) * 128; // a third of the quadrant's columns
+  P.tmem_tw = tmem_quad + V3_TW_COL;
+  return P;
+}
+
 // One CMUX of one polynomial (one warp).  Kept out of line on purpose: with 128 of the 168
 // registers holding the 32 complex points, the loop state of the caller (round, sample, LWE
 // pointer, counters) must not stay live across the transforms; everything the body needs beyond
 // its three arguments is re-derived from the thread index or read from the control block.
-__device__ __noinline__ void v3_cmux(const u32 a_hat, const u32 t0, const u32 i) {
+__device__ __noinline__ void v3_cmux(const u32 a_hat) {
   extern __shared__ __align__(1024) unsigned char smem[];
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int r = warp & 1;
-  V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
-  const u32 buf_s = smem_u32(smem) + (u32)warp * V3_BUF_BYTES;
-  V3Addr A;
-  A.rowb = buf_s + 512u * lane;
-  A.colb = buf_s + 16u * lane;
-  A.l7s = (lane & 7) << 4;
-  const u32 tmem_quad = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16);
-  const u32 tmem_own = tmem_quad + (u32)(warp >> 2) * 128; // a third of the quadrant's columns
-  const u32 tmem_tw = tmem_quad + V3_TW_COL;
-
   double2 x[32];
   { // ct1 = ACC*X^a - ACC, closest_representable, signed digit (l = 1) -> doubles
+    const V3Phase P = v3_phase();
+    V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
     const u32 kshift = 32 - ctrl->base_log;
     // 16 * ((lane - a_hat) mod 4096): bits 4..13 address the pair, bit 14 swaps (re, im), bit 15
     // negates re, bit 14 ^ bit 15 negates im  (multiplication by (-i)^q, q = bits 15:14)
-    const u32 s16 = ((u32)(lane - (int)a_hat) << 4) & 0xFFF0u;
+    const u32 s16 = ((u32)(P.lane - (int)a_hat) << 4) & 0xFFF0u;
     u32 va[16], vb[16];
-    tmem_ld16(tmem_own, va);
+    tmem_ld16(P.tmem_own, va);
     tmem_wait_ld();
 #pragma unroll
     for (int cc = 0; cc < 4; ++cc) {
-      tmem_ld16(tmem_own + 16 * (2 * cc + 1), vb);
-      v3_digits<0>(x, va, 2 * cc, s16, buf_s, kshift);
+      tmem_ld16(P.tmem_own + 16 * (2 * cc + 1), vb);
+      v3_digits<0>(x, va, 2 * cc, s16, P.buf_s, kshift);
       tmem_wait_ld();
-      if (cc < 3) tmem_ld16(tmem_own + 16 * (2 * cc + 2), va);
-      v3_digits<0>(x, vb, 2 * cc + 1, s16, buf_s, kshift);
+      if (cc < 3) tmem_ld16(P.tmem_own + 16 * (2 * cc + 2), va);
+      v3_digits<0>(x, vb, 2 * cc + 1, s16, P.buf_s, kshift);
       if (cc < 3) tmem_wait_ld();
     }
   }
 
   fwd_pass1(x);
   __syncwarp(); // rotated reads of the accumulator are done in every lane
-#pragma unroll
-  for (int p = 0; p < 32; ++p) sts128(v3_col(A, p), x[p]);
-  __syncwarp();
-#pragma unroll
-  for (int p = 0; p < 32; ++p) x[p] = lds128(v3_row(A, p));
   {
-    u32 v[16];
-    tmem_ld16(tmem_tw, v);
-    tmem_wait_ld();
-    v3_fwd_stages012(x, v);
+    const V3Phase P = v3_phase();
+    st_col_all<0>(P.A, x);
+    __syncwarp();
+    ld_row_all<0>(P.A, x);
+    v3_fwd_stages012(x, P.tmem_tw);
   }
 
   __syncwarp(); // transpose reads of the buffer are done in every lane
   {
-    const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * lane;
-    u32 tv[8];
-    tmem_ld8(tmem_tw + 16, tv);
-    v3_fwd_group<0>(x, tv, 0, A, tmem_tw, key + (r * 2 + r) * 2048,
-                    key + (r * 2 + (1 - r)) * 2048, t0, i, lane);
+    const V3Phase P = v3_phase();
+    const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * P.lane + (P.warp & 1) * 4096;
+    v3_fwd_group<0>(x, P.A, P.tmem_tw, key, P.lane);
   }
-
-  asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp >> 1)) : "memory");
-  v3_inv_group<0>(x, A, tmem_tw, r ? 0u - V3_BUF_BYTES : V3_BUF_BYTES);
-  asm volatile("bar.sync %0, 64;" ::"r"(1 + (warp >> 1)) : "memory"); // partner done with buf
   {
-    u32 v[16];
-    tmem_ld16(tmem_tw, v);
-    tmem_wait_ld();
-    v3_inv_stages210(x, v);
+    const V3Phase P = v3_phase();
+    const int r = P.warp & 1;
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + (P.warp >> 1)) : "memory");
+    v3_inv_group<0>(x, P.A, P.tmem_tw, r ? 0u - V3_BUF_BYTES : V3_BUF_BYTES);
+    asm volatile("bar.sync %0, 64;" ::"r"(1 + (P.warp >> 1)) : "memory"); // partner done with buf
   }
-#pragma unroll
-  for (int p = 0; p < 32; ++p) sts128(v3_row(A, p), x[p]);
-  __syncwarp();
-#pragma unroll
-  for (int p = 0; p < 32; ++p) x[p] = lds128(v3_col(A, p));
+  {
+    const V3Phase P = v3_phase();
+    v3_inv_stages210(x, P.tmem_tw);
+    st_row_all<0>(P.A, x);
+    __syncwarp();
+    ld_col_all<0>(P.A, x);
+  }
   inv_pass1(x);
 
+  const V3Phase P = v3_phase();
+  const int lane = P.lane, warp = P.warp;
+  const u32 tmem_own = P.tmem_own;
   // ACC += round(x): own copy from TMEM; the new value goes back to TMEM and to the shared
   // home for the rotated read of the next CMUX
   __syncwarp(); // transpose reads of the buffer are done before it becomes the accumulator again
@@ -546,16 +648,24 @@ __global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a
     }
     __syncwarp();
 
-    u32 a_next = active ? modulus_switch(__ldg(&lwe[0]), LOGM + 2) : 0;
+    // mod-switched mask elements, 32 at a time: lane k holds a_hat[i0 + k] (one coalesced load
+    // per 32 CMUXes instead of a global-load latency in front of every out-of-line call)
+    u32 a_blk = 0;
 #pragma unroll 1
     for (u32 i = 0; i < n; ++i, ++cmux) {
-      const u32 a_hat = a_next;
-      if (active && i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), LOGM + 2);
-      const u32 t0 = cmux * V3_GROUPS;
+      if ((i & 31) == 0) {
+        const u32 k = i + lane;
+        a_blk = (active && k < n) ? modulus_switch(__ldg(&lwe[k]), LOGM + 2) : 0;
+      }
+      const u32 a_hat = __shfl_sync(0xffffffffu, a_blk, i & 31);
+      if (lane == 0) { // what the refill path needs to know about this warp's CMUX
+        ctrl->wt0[warp] = cmux * V3_GROUPS;
+        ctrl->wi[warp] = i;
+      }
       if (a_hat == 0) // X^0 - 1 = 0: no CMUX (bootstrap.rs:287); still walk the ring
-        v3_idle_groups<0>(t0, i, lane);
+        v3_idle_groups<0>(lane);
       else
-        v3_cmux(a_hat, t0, i);
+        v3_cmux(a_hat);
     }
 
     // sample extraction: warp 0 of the pair holds the mask polynomial, warp 1 the body
