@@ -226,6 +226,10 @@ void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, cons
     CB_LAUNCHED();
   }
   const size_t smem = (size_t)KT * BS * 4 + (size_t)KT * BO * 8;
+  // KT = 48 (e.g. l_ks = 6, 12, 16, 24) needs 48 KiB dynamic + 1 KiB static: above the default
+  // 48 KiB per-CTA limit, so the kernel always opts in to its maximum (MAX_KT rows)
+  CB_CHECK(cudaFuncSetAttribute(ks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)((size_t)MAX_KT * BS * 4 + (size_t)MAX_KT * BO * 8)));
   ks_kernel<<<grid, NT, smem, stream>>>(out, out_idx, in, in_idx, ksk, n_in, n_out, base_log,
                                         level, num_samples, KI, tiles_per_split, use_atomics);
   CB_CHECK(cudaGetLastError());

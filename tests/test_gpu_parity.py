@@ -88,6 +88,26 @@ def test_keyswitch_edge_values_and_indexes(engine):
     assert np.array_equal(got, ref)
 
 
+@pytest.mark.parametrize("n_in,n_out,b_ks,l_ks,num", [
+    (8192, 915, 3, 6, 130),    # P7's shape: 48 kappa rows per tile (48 KiB + static shared memory)
+    (16384, 1006, 4, 5, 40),   # P8's shape
+    (700, 333, 1, 1, 5), (700, 333, 2, 12, 200), (513, 64, 2, 16, 129), (300, 63, 1, 48, 3),
+    (1024, 599, 31, 2, 77), (2048, 742, 7, 7, 1), (96, 1000, 9, 7, 260)])
+def test_keyswitch_decomposition_shapes(engine, n_in, n_out, b_ks, l_ks, num):
+    """Every tile configuration of the kernel (inputs per tile = min(8, 48 / l_ks)), split-K on and
+    off, ragged edges in all three dimensions.  The keyswitch is linear algebra over wrapping u64,
+    so a uniformly random "KSK" checks the arithmetic word for word against the oracle."""
+    from concrete_b200 import as_u64
+
+    rng = np.random.default_rng(n_in + 31 * l_ks)
+    ksk = rng.integers(0, 2 ** 64, size=n_in * l_ks * (n_out + 1), dtype=np.uint64)
+    cts = rng.integers(0, 2 ** 64, size=(num, n_in + 1), dtype=np.uint64)
+    ref = orc.keyswitch(cts, ksk, n_in, n_out, b_ks, l_ks)
+    got = as_u64(engine.keyswitch(engine.to_device(cts), engine.upload_ksk(ksk), n_in, n_out,
+                                  b_ks, l_ks))
+    assert np.array_equal(got, ref)
+
+
 def test_keyswitch_empty_batch(engine):
     import torch
 
