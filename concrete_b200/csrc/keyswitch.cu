@@ -17,6 +17,8 @@
 // summation order (incl. the split-K atomics used for small batches) is bit-exact.
 #include "common.cuh"
 #include "../../include/concrete_b200.h"
+#include <algorithm>
+#include <string>
 
 namespace {
 
@@ -191,6 +193,70 @@ ks_kernel(u64 *__restrict__ out, const u64 *__restrict__ out_idx, const u64 *__r
 }
 
 } // namespace
+#include "keyswitch_imma.cuh"
+#include <cstdlib>
+
+namespace {
+
+// Tensor-core path (keyswitch_imma.cuh).  Chosen when the batch fills the GEMM tiles and the
+// exactness conditions hold: digits fit s8 (|d| <= B/2 <= 64) and the s32 accumulators cannot
+// wrap (B/2 * 255 * K < 2^31).  Otherwise the IMAD kernel below runs; both are bit-exact.
+bool ks_imma_eligible(u32 n_in, u32 base_log, u32 level, u32 num_samples) {
+  static const char *env = std::getenv("CONCRETE_B200_KS");
+  if (env && std::string(env) == "imad") return false;
+  const bool forced = env && std::string(env) == "imma";
+  if (base_log > 7) return false;
+  const u64 K = (u64)n_in * level;
+  if ((K << (base_log - 1)) * 255 >= ((u64)1 << 31)) return false;
+  return forced || num_samples >= 512;
+}
+
+void ks_imma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
+                    const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
+                    u32 level, u32 num_samples) {
+  const u32 K = n_in * level, out_size = n_out + 1;
+  const u32 Kp = (K + imma::TK - 1) / imma::TK * imma::TK;
+  const u32 Np = (out_size * 8 + imma::TN - 1) / imma::TN * imma::TN;
+  // samples per chunk: digit scratch <= 256 MiB, whole tiles
+  u32 chunk = (u32)std::min<u64>(((u64)256 << 20) / Kp, (u64)num_samples + imma::TM - 1);
+  chunk = std::max<u32>(imma::TM, chunk / imma::TM * imma::TM);
+  unsigned char *Bt = nullptr;
+  signed char *D = nullptr;
+  CB_CHECK(cudaMallocAsync((void **)&Bt, (size_t)Np * Kp, stream));
+  CB_CHECK(cudaMallocAsync((void **)&D, (size_t)chunk * Kp, stream));
+  {
+    dim3 grid((Np / 8 + 31) / 32, Kp / 64);
+    imma::ks_planes_kernel<<<grid, 256, 0, stream>>>(Bt, ksk, K, out_size, Kp, Np / 8);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+  }
+  static bool attr_set[64] = {};
+  int dev = 0;
+  CB_CHECK(cudaGetDevice(&dev));
+  if (!attr_set[dev & 63]) {
+    CB_CHECK(cudaFuncSetAttribute(imma::ks_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  imma::SMEM_BYTES));
+    attr_set[dev & 63] = true;
+  }
+  for (u32 s0 = 0; s0 < num_samples; s0 += chunk) {
+    const u32 count = std::min(chunk, num_samples - s0);
+    const u32 rows = (count + imma::TM - 1) / imma::TM * imma::TM;
+    dim3 gd(std::min<u32>((n_in + 255) / 256, 8), rows);
+    imma::ks_digits_kernel<<<gd, 256, 0, stream>>>(D, in, in_idx, n_in, base_log, level, s0,
+                                                   count, Kp);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    dim3 gg(Np / imma::TN, rows / imma::TM);
+    imma::ks_imma_kernel<<<gg, imma::NT, imma::SMEM_BYTES, stream>>>(
+        out, out_idx, in, in_idx, D, Bt, n_in, n_out, s0, count, Kp);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+  }
+  CB_CHECK(cudaFreeAsync(D, stream));
+  CB_CHECK(cudaFreeAsync(Bt, stream));
+}
+
+} // namespace
 
 void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
                          const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
@@ -201,6 +267,11 @@ void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, cons
              level);
   if (level > MAX_KT)
     CB_PANIC("Cuda error (keyswitch): level_count %u > %d unsupported", level, MAX_KT);
+  if (ks_imma_eligible(n_in, base_log, level, num_samples)) {
+    ks_imma_launch(stream, out, out_idx, in, in_idx, ksk, n_in, n_out, base_log, level,
+                   num_samples);
+    return;
+  }
   u32 KI = MAX_KT / level;
   if (KI > 8) KI = 8;
   if (KI < 1) KI = 1;

@@ -57,14 +57,14 @@ def test_keyswitch_bit_exact(engine, name, num):
     assert np.array_equal(ks.decrypt_small(got, bits), msgs)
 
 
-def test_keyswitch_edge_values_and_indexes(engine):
+@pytest.mark.parametrize("num", [64, 640])  # IMAD kernel / INT8 tensor-core kernel
+def test_keyswitch_edge_values_and_indexes(engine, num):
     """a_i in {0, 2^63, 2^64-1, exact half-way rounding points}; permuted in/out index arrays."""
     import torch
     from concrete_b200 import as_u64
 
     ks = keyset("TOY512")
     p = ks.p
-    num = 64
     rng = np.random.default_rng(5)
     cts = rng.integers(0, 2 ** 64, size=(num, p.big_n + 1), dtype=np.uint64)
     shift = 64 - p.b_ks * p.l_ks
@@ -92,11 +92,17 @@ def test_keyswitch_edge_values_and_indexes(engine):
     (8192, 915, 3, 6, 130),    # P7's shape: 48 kappa rows per tile (48 KiB + static shared memory)
     (16384, 1006, 4, 5, 40),   # P8's shape
     (700, 333, 1, 1, 5), (700, 333, 2, 12, 200), (513, 64, 2, 16, 129), (300, 63, 1, 48, 3),
-    (1024, 599, 31, 2, 77), (2048, 742, 7, 7, 1), (96, 1000, 9, 7, 260)])
+    (1024, 599, 31, 2, 77), (2048, 742, 7, 7, 1), (96, 1000, 9, 7, 260),
+    # batches >= 512 take the INT8 tensor-core path when digits fit s8 and s32 sums cannot wrap
+    (2048, 742, 3, 5, 700), (2048, 801, 4, 3, 513), (16384, 1006, 4, 5, 520), (8192, 915, 3, 6, 640),
+    (333, 15, 7, 9, 1025), (77, 130, 1, 3, 512), (1000, 500, 2, 20, 600),
+    (700, 333, 9, 7, 600),      # digits do not fit s8 -> IMAD kernel at a large batch
+    (40000, 16, 7, 9, 512)])    # (B/2) * 255 * K >= 2^31 -> IMAD kernel
 def test_keyswitch_decomposition_shapes(engine, n_in, n_out, b_ks, l_ks, num):
-    """Every tile configuration of the kernel (inputs per tile = min(8, 48 / l_ks)), split-K on and
-    off, ragged edges in all three dimensions.  The keyswitch is linear algebra over wrapping u64,
-    so a uniformly random "KSK" checks the arithmetic word for word against the oracle."""
+    """Every tile configuration of both keyswitch kernels (IMAD: inputs per tile = min(8, 48 /
+    l_ks), split-K on and off; INT8-MMA: ragged edges in all three GEMM dimensions).  The
+    keyswitch is linear algebra over wrapping u64, so a uniformly random "KSK" checks the
+    arithmetic word for word against the oracle."""
     from concrete_b200 import as_u64
 
     rng = np.random.default_rng(n_in + 31 * l_ks)
