@@ -17,6 +17,7 @@
 #include "../../include/concrete_b200_runtime.h"
 #include <cstdint>
 #include <cstdlib>
+#include <cuda_runtime.h>
 #include <memory>
 #include <mutex>
 #include <vector>
@@ -48,6 +49,10 @@ struct GpuSlot {
   int8_t *pbs_buffer = nullptr;
   uint32_t pbs_k = 0, pbs_N = 0, pbs_l = 0, pbs_count = 0;
   std::vector<uint64_t> host_idx; // staging for lut indexes (must outlive the async copy)
+  // copy/compute overlap inside one batched call: chunk c+1 uploads and chunk c-1 downloads while
+  // chunk c computes (two extra streams on the two copy engines, one event pair per chunk)
+  void *h2d_stream = nullptr, *d2h_stream = nullptr;
+  std::vector<cudaEvent_t> ev_in, ev_done;
 };
 
 typedef struct RuntimeContext {
@@ -81,6 +86,10 @@ typedef struct RuntimeContext {
         if (s.pbs_buffer) cleanup_cuda_programmable_bootstrap(s.stream, i, &s.pbs_buffer);
         for (DevBuf *b : {&s.ct_in, &s.ct_mid, &s.ct_out, &s.lut, &s.lut_idx, &s.iota})
           if (b->ptr) cuda_drop(b->ptr, i);
+        if (s.h2d_stream) cuda_destroy_stream(s.h2d_stream, i);
+        if (s.d2h_stream) cuda_destroy_stream(s.d2h_stream, i);
+        for (auto &v : {&s.ev_in, &s.ev_done})
+          for (cudaEvent_t e : *v) cudaEventDestroy(e);
         cuda_destroy_stream(s.stream, i);
       }
     }

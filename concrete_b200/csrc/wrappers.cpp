@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 #include <functional>
 #include <thread>
+#include <vector>
 
 using mlir::concretelang::DevBuf;
 using mlir::concretelang::GpuSlot;
@@ -112,6 +113,76 @@ void *upload_luts(GpuSlot &s, const uint64_t *tlu, uint64_t num_luts, uint64_t t
   return d;
 }
 
+// Chunk boundaries of one shard for the copy/compute pipeline: up to 4 chunks, each a whole
+// number of `quantum` samples (one wave of the persistent PBS grid / one GEMM tile row), so that
+// chunking adds no partially filled wave.  Small batches stay one chunk.
+std::vector<uint64_t> chunk_bounds(uint64_t cnt, uint64_t quantum) {
+  std::vector<uint64_t> b{0};
+  if (cnt < 4 * quantum) {
+    b.push_back(cnt);
+    return b;
+  }
+  const uint64_t per = ((cnt + 3) / 4 + quantum - 1) / quantum * quantum;
+  for (uint64_t o = per; o < cnt; o += per) b.push_back(o);
+  b.push_back(cnt);
+  return b;
+}
+
+void ensure_pipe(GpuSlot &s, size_t chunks) {
+  W_CHECK(cudaSetDevice(s.gpu));
+  if (!s.h2d_stream) s.h2d_stream = cuda_create_stream(s.gpu);
+  if (!s.d2h_stream) s.d2h_stream = cuda_create_stream(s.gpu);
+  while (s.ev_in.size() < chunks) {
+    cudaEvent_t a, b;
+    W_CHECK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+    W_CHECK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+    s.ev_in.push_back(a);
+    s.ev_done.push_back(b);
+  }
+}
+
+// H2D of every chunk on the upload stream, compute(chunk) on the slot's stream once its input
+// landed, D2H of the chunk on the download stream once it is computed; returns after all three
+// streams drained.  in/out rows are in_w / out_w words.
+void run_pipelined(GpuSlot &s, const std::vector<uint64_t> &bounds, const uint64_t *h_in,
+                   uint64_t in_w, void *d_in, uint64_t *h_out, uint64_t out_w, void *d_out,
+                   const std::function<void(uint64_t off, uint64_t n)> &compute) {
+  const size_t C = bounds.size() - 1;
+  const uint32_t gpu = s.gpu;
+  if (C == 1) {
+    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(h_in), bounds[1] * in_w * 8, s.stream, gpu);
+    compute(0, bounds[1]);
+    cuda_memcpy_async_to_cpu(h_out, d_out, bounds[1] * out_w * 8, s.stream, gpu);
+    cuda_synchronize_stream(s.stream, gpu);
+    return;
+  }
+  ensure_pipe(s, C);
+  // whatever the slot's stream still holds (key conversion, LUT upload) precedes the pipeline
+  for (size_t c = 0; c < C; ++c) {
+    const uint64_t off = bounds[c], n = bounds[c + 1] - off;
+    cuda_memcpy_async_to_gpu((uint64_t *)d_in + off * in_w, const_cast<uint64_t *>(h_in + off * in_w),
+                             n * in_w * 8, s.h2d_stream, gpu);
+    W_CHECK(cudaEventRecord(s.ev_in[c], (cudaStream_t)s.h2d_stream));
+  }
+  for (size_t c = 0; c < C; ++c) {
+    const uint64_t off = bounds[c], n = bounds[c + 1] - off;
+    W_CHECK(cudaStreamWaitEvent((cudaStream_t)s.stream, s.ev_in[c], 0));
+    compute(off, n);
+    W_CHECK(cudaEventRecord(s.ev_done[c], (cudaStream_t)s.stream));
+    W_CHECK(cudaStreamWaitEvent((cudaStream_t)s.d2h_stream, s.ev_done[c], 0));
+    cuda_memcpy_async_to_cpu(h_out + off * out_w, (uint64_t *)d_out + off * out_w, n * out_w * 8,
+                             s.d2h_stream, gpu);
+  }
+  cuda_synchronize_stream(s.d2h_stream, gpu);
+  cuda_synchronize_stream(s.stream, gpu);
+}
+
+uint64_t pbs_wave(uint32_t gpu) { // samples per wave of the persistent PBS grid (6 per SM)
+  int sms = 148;
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, (int)gpu);
+  return (uint64_t)sms * 6;
+}
+
 void bootstrap_impl(uint64_t *out, const uint64_t *ct0, uint64_t num_samples, uint64_t ct0_size1,
                     uint64_t out_size1, const uint64_t *tlu, uint64_t num_luts,
                     uint64_t tlu_row_stride, uint32_t input_lwe_dim, uint32_t poly_size,
@@ -125,8 +196,6 @@ void bootstrap_impl(uint64_t *out, const uint64_t *ct0, uint64_t num_samples, ui
                                       bsk_index);
     void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
     void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
-    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
-                             cnt * ct0_size1 * 8, s.stream, gpu);
     void *d_lut, *d_lut_idx;
     if (num_luts == 1) {
       d_lut = upload_luts(s, tlu, 1, tlu_row_stride, glwe_dim, poly_size);
@@ -140,11 +209,14 @@ void bootstrap_impl(uint64_t *out, const uint64_t *ct0, uint64_t num_samples, ui
     }
     void *iota = get_iota(s, (uint32_t)cnt);
     ensure_pbs(s, glwe_dim, poly_size, level, (uint32_t)cnt);
-    cuda_programmable_bootstrap_lwe_ciphertext_vector_64(
-        s.stream, gpu, d_out, iota, d_lut, d_lut_idx, d_in, iota, fbsk, s.pbs_buffer,
-        input_lwe_dim, glwe_dim, poly_size, base_log, level, (uint32_t)cnt, 1, 1);
-    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
-    cuda_synchronize_stream(s.stream, gpu);
+    run_pipelined(s, chunk_bounds(cnt, pbs_wave(gpu)), ct0 + begin * ct0_size1, ct0_size1, d_in,
+                  out + begin * out_size1, out_size1, d_out, [&](uint64_t off, uint64_t n) {
+                    cuda_programmable_bootstrap_lwe_ciphertext_vector_64(
+                        s.stream, gpu, (uint64_t *)d_out + off * out_size1, iota, d_lut,
+                        (uint64_t *)d_lut_idx + off, (uint64_t *)d_in + off * ct0_size1, iota, fbsk,
+                        s.pbs_buffer, input_lwe_dim, glwe_dim, poly_size, base_log, level,
+                        (uint32_t)n, 1, 1);
+                  });
   });
 }
 
@@ -192,14 +264,14 @@ void memref_batched_keyswitch_lwe_cuda_u64(
     void *ksk = context->get_ksk_gpu(level, input_lwe_dim, output_lwe_dim, gpu, s.stream, ksk_index);
     void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
     void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
-    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
-                             cnt * ct0_size1 * 8, s.stream, gpu);
     void *iota = get_iota(s, (uint32_t)cnt);
-    cuda_keyswitch_lwe_ciphertext_vector_64(s.stream, gpu, d_out, iota, d_in, iota, ksk,
-                                            input_lwe_dim, output_lwe_dim, base_log, level,
-                                            (uint32_t)cnt);
-    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
-    cuda_synchronize_stream(s.stream, gpu);
+    run_pipelined(s, chunk_bounds(cnt, 1024), ct0 + begin * ct0_size1, ct0_size1, d_in,
+                  out + begin * out_size1, out_size1, d_out, [&](uint64_t off, uint64_t n) {
+                    cuda_keyswitch_lwe_ciphertext_vector_64(
+                        s.stream, gpu, (uint64_t *)d_out + off * out_size1, iota,
+                        (uint64_t *)d_in + off * ct0_size1, iota, ksk, input_lwe_dim,
+                        output_lwe_dim, base_log, level, (uint32_t)n);
+                  });
   });
 }
 

@@ -495,6 +495,38 @@ def test_memref_wrappers_host_buffers(engine):
     rt.close()
 
 
+def test_memref_wrappers_pipelined_chunks(engine):
+    """Batches large enough for the wrappers' copy/compute pipeline (several chunks, ragged last
+    chunk; wrappers.cpp::run_pipelined): the keyswitch words equal the oracle's for every sample,
+    every PBS decrypts to LUT[m], and the mapped form picks each sample's own table across chunk
+    boundaries."""
+    from concrete_b200.runtime import Runtime
+
+    ks = keyset("TOY1024")
+    p = ks.p
+    bits, num = 3, 4 * 888 + 333
+    table = (np.arange(8) ** 2 % 8).astype(np.uint64)
+    lut_poly = expand_lut(table, p.N, bits)
+    rng = np.random.default_rng(17)
+    msgs = rng.integers(0, 8, num).astype(np.uint64)
+    cts = ks.encrypt_big(msgs, bits)
+    rt = Runtime(num_gpus=1)
+    ki, bi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk)
+    ref_mid = orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    mid = np.zeros((num, p.n + 1), dtype=np.uint64)
+    out = np.zeros((num, p.big_n + 1), dtype=np.uint64)
+    rt.batched_keyswitch(mid, cts, p.l_ks, p.b_ks, p.big_n, p.n, ki)
+    assert np.array_equal(mid, ref_mid)
+    rt.batched_bootstrap(out, mid, lut_poly, p.n, p.N, p.l, p.b, p.k, bi)
+    assert np.array_equal(ks.decrypt_big(out, bits), table[msgs])
+    tables = np.stack([np.roll(table, s % 8) for s in range(num)])
+    tlus = np.stack([expand_lut(t, p.N, bits) for t in tables])
+    out = np.zeros((num, p.big_n + 1), dtype=np.uint64)
+    rt.batched_mapped_bootstrap(out, ref_mid, tlus, p.n, p.N, p.l, p.b, p.k, bi)
+    assert np.array_equal(ks.decrypt_big(out, bits), tables[np.arange(num), msgs])
+    rt.close()
+
+
 # ----------------------------------------------------------- full-size properties (cfg 2 shape)
 def test_full_size_batch_properties(engine):
     """BASELINE.json configs[1] size (16 384 ciphertexts, P2048): too big for the oracle, so check
