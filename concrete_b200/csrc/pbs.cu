@@ -517,8 +517,7 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
       auto kern = w32::pbs_kernel_w32v3;
       CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)w32::SMEM_BYTES3));
-      const u32 ctas = (num_samples + w32::CPB3 - 1) / w32::CPB3;
-      const u32 grid = std::min<u32>((u32)sms, ctas);
+      const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
       kern<<<grid, w32::NTHREADS3, w32::SMEM_BYTES3, stream>>>(a);
     }
     CB_CHECK(cudaGetLastError());

@@ -548,10 +548,17 @@ __global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a
   const u32 n = a.n;
   const size_t out_size = (size_t)N + 1;
 
-  const u32 round_stride = gridDim.x * CPB3;
-  const u32 first = blockIdx.x * CPB3;
-  const u32 rounds =
-      (first < a.num_samples) ? (a.num_samples - first + round_stride - 1) / round_stride : 0;
+  // Sample -> (CTA, round, slot): `full` rounds in which every CTA holds CPB3 ciphertexts, then
+  // the remainder spread evenly over ALL CTAs in one last round (a round with fewer active
+  // ciphertexts is shorter: idle warps only walk the key ring), so small batches use every SM
+  // and the tail of a large batch costs a fraction of a round.
+  const u32 wave = gridDim.x * CPB3;
+  const u32 full = a.num_samples / wave;
+  const u32 rem = a.num_samples - full * wave;
+  const u32 rem_base = rem / gridDim.x, rem_extra = rem % gridDim.x;
+  const u32 my_rem = rem_base + (blockIdx.x < rem_extra ? 1u : 0u);
+  const u32 rem_first = full * wave + blockIdx.x * rem_base + min(blockIdx.x, rem_extra);
+  const u32 rounds = full + (my_rem ? 1u : 0u);
   const u32 total_fills = rounds * n * V3_GROUPS;
 
   if (tid == 0) {
@@ -615,8 +622,8 @@ __global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a
 
   u32 cmux = 0; // CMUX rounds of this CTA so far (every warp sees every one of them)
   for (u32 rd = 0; rd < rounds; ++rd) {
-    const u32 sample = first + rd * round_stride + ct;
-    const bool active = sample < a.num_samples;
+    const bool active = rd < full || (u32)ct < my_rem;
+    const u32 sample = rd < full ? rd * wave + blockIdx.x * CPB3 + ct : rem_first + ct;
     const u64 *lwe = a.lwe_in + (active ? a.in_idx[sample] : 0) * (u64)(n + 1);
 
     if (active) {
