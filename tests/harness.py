@@ -61,7 +61,8 @@ def expand_lut(table: np.ndarray, N: int, out_bits: int) -> np.ndarray:
     shift = np.uint64(64 - out_bits - 1)
     out = np.zeros(N, dtype=np.uint64)
     out[: mega // 2] = table[0] << shift
-    out[(size - 1) * mega + mega // 2:] = (np.uint64(0) - (table[0] << shift))
+    with np.errstate(over="ignore"):  # wrapping negation on purpose
+        out[(size - 1) * mega + mega // 2:] = (np.uint64(0) - (table[0] << shift))
     for i in range(1, size):
         s = mega * (i - 1) + mega // 2
         out[s: s + mega] = table[i] << shift

@@ -182,3 +182,38 @@ def test_cfg5_chunked_16bit_add(engine):
     total = sum(low[:, c] << (2 * c) for c in range(chunks))
     assert np.array_equal(total, (a + b) & 0xFFFF)
     assert np.array_equal(ks.decrypt_big(as_u64(d_carry), bits).astype(np.int64), (a + b) >> 16)
+
+
+def test_wrappers_sharded_over_two_gpus(engine):
+    """the batched wrappers shard a batch over SDFG_NUM_GPUS devices (contiguous
+    split, one host thread + stream per device, keys uploaded/converted per device, no collective
+    in the data path).  Needs a box with >= 2 GPUs; the split rule itself is covered on CPU by
+    tests/test_host_logic.py."""
+    import torch
+    from concrete_b200.runtime import Runtime
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ks = KeySet(PARAMS["TOY1024"], seed=42)
+    p = ks.p
+    bits, num = 3, 2 * 888 * 2 + 101                      # odd split, pipelined chunks on each GPU
+    table = (np.arange(8) ** 2 % 8).astype(np.uint64)
+    lut_poly = expand_lut(table, p.N, bits)
+    rng = np.random.default_rng(23)
+    msgs = rng.integers(0, 8, num).astype(np.uint64)
+    cts = ks.encrypt_big(msgs, bits)
+    ref_mid = orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    rt = Runtime(num_gpus=2)
+    ki, bi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk)
+    mid = np.zeros((num, p.n + 1), dtype=np.uint64)
+    out = np.zeros((num, p.big_n + 1), dtype=np.uint64)
+    rt.batched_keyswitch(mid, cts, p.l_ks, p.b_ks, p.big_n, p.n, ki)
+    assert np.array_equal(mid, ref_mid)
+    rt.batched_bootstrap(out, mid, lut_poly, p.n, p.N, p.l, p.b, p.k, bi)
+    assert np.array_equal(ks.decrypt_big(out, bits), table[msgs])
+    tables = np.stack([np.roll(table, s % 8) for s in range(num)])
+    tlus = np.stack([expand_lut(t, p.N, bits) for t in tables])
+    out = np.zeros((num, p.big_n + 1), dtype=np.uint64)
+    rt.batched_mapped_bootstrap(out, ref_mid, tlus, p.n, p.N, p.l, p.b, p.k, bi)
+    assert np.array_equal(ks.decrypt_big(out, bits), tables[np.arange(num), msgs])
+    rt.close()
