@@ -364,20 +364,30 @@ __device__ __forceinline__ void v3_product(double2 (&x)[32], const V3Addr &A, u3
 // place, cross term to the partner warp through this warp's buffer).  Software pipelined across
 // groups: on entry tv holds the twiddles of G (tcgen05.ld in flight) and `tried` the result of
 // an early try_wait on the fill of G; the body issues both for G + 1 under its own arithmetic.
+// wait for the TMEM loads in flight; ta/tb are operands so that every later use reads them after
+// the wait (the loads that fill them were issued one group earlier)
+__device__ __forceinline__ void tmem_wait_ld8(u32 (&ta)[4], u32 (&tb)[4]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(ta[0]), "+r"(ta[1]), "+r"(ta[2]), "+r"(ta[3]), "+r"(tb[0]), "+r"(tb[1]),
+                 "+r"(tb[2]), "+r"(tb[3])
+               :
+               : "memory");
+}
 template <int G>
 __device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], const V3Addr &A, u32 tmem_tw,
-                                             u32 keyr, int lane) {
+                                             u32 keyr, int lane, u32 (&ta)[4], u32 (&tb)[4]) {
   {
-    u32 ta[4], tb[4];
-    tmem_ld4(tmem_tw + 16 + 8 * G, ta);
-    tmem_ld4(tmem_tw + 20 + 8 * G, tb);
-    tmem_wait_ld();
+    tmem_wait_ld8(ta, tb); // twiddles of group G, loaded under the products of group G - 1
     const double2 t4 = tw_of(ta);
     const double2 t3 = (G & 1) ? mul_i(tw_of(tb)) : tw_of(tb);
     cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 2], t3);
     cbfft::bfly_ct(x[4 * G + 1], x[4 * G + 3], t3);
     cbfft::bfly_ct(x[4 * G + 0], x[4 * G + 1], t4);
     cbfft::bfly_ct(x[4 * G + 2], x[4 * G + 3], mul_i(t4));
+    if constexpr (G + 1 < V3_GROUPS) { // t3/t4 are dead: refill the same registers for G + 1
+      tmem_ld4(tmem_tw + 16 + 8 * (G + 1), ta);
+      tmem_ld4(tmem_tw + 20 + 8 * (G + 1), tb);
+    }
   }
   v3_wait_full<G>(0);
   constexpr u32 so = (G & (V3_SLOTS - 1)) * V3_SLOT_BYTES;
@@ -393,7 +403,7 @@ __device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], const V3Addr &A, 
     x[p] = cmul(x[p], w);
   }
   v3_refill<G>(old, lane);
-  if constexpr (G + 1 < V3_GROUPS) v3_fwd_group<G + 1>(x, A, tmem_tw, keyr, lane);
+  if constexpr (G + 1 < V3_GROUPS) v3_fwd_group<G + 1>(x, A, tmem_tw, keyr, lane, ta, tb);
 }
 
 // inverse group G: add the partner's cross term, inverse stages s2 = 4,3
@@ -494,7 +504,10 @@ __device__ __noinline__ void v3_cmux(const u32 a_hat) {
   {
     const V3Phase P = v3_phase();
     const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * P.lane + (P.warp & 1) * 4096;
-    v3_fwd_group<0>(x, P.A, P.tmem_tw, key, P.lane);
+    u32 ta[4], tb[4];
+    tmem_ld4(P.tmem_tw + 16, ta);
+    tmem_ld4(P.tmem_tw + 20, tb);
+    v3_fwd_group<0>(x, P.A, P.tmem_tw, key, P.lane, ta, tb);
   }
   {
     const V3Phase P = v3_phase();
