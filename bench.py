@@ -259,12 +259,15 @@ def run_ours(args):
         sampler.start()
     launches0 = lib.concrete_b200_kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         step()
+        marks[i].record()
     e1.record()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
+    step_ms = [round(a.elapsed_time(b), 2) for a, b in zip([e0] + marks[:-1], marks)]  # rank 0
     launches = int(lib.concrete_b200_kernel_launches() - launches0)
     ms_step = ms_total / args.steps
     value = world * S / (ms_step * 1e-3)
@@ -409,7 +412,7 @@ def run_ours(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
             "data": "synthetic (seed 42 keys and ciphertexts, valid encryptions)",
             "config": workload_config(p, S, world),
-            "us_per_pbs": ms_step * 1e3 / S, "gpu_launches": launches,
+            "us_per_pbs": ms_step * 1e3 / S, "step_ms_rank0": step_ms, "gpu_launches": launches,
             "verified_decryptions": verified, "clocks": clocks, "roofline": roofline,
             "e2e": e2e, "cpu_baseline": cpu, "reference_gpu": ref_gpu_line,
         }

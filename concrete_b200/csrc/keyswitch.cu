@@ -18,6 +18,7 @@
 #include "common.cuh"
 #include "../../include/concrete_b200.h"
 #include <algorithm>
+#include <mutex>
 #include <string>
 
 namespace {
@@ -211,6 +212,26 @@ bool ks_imma_eligible(u32 n_in, u32 base_log, u32 level, u32 num_samples) {
   return forced || num_samples >= 512;
 }
 
+cudaMemPool_t ks_scratch_pool() {
+  static std::mutex mu;
+  static cudaMemPool_t pools[64] = {};
+  int dev = 0;
+  CB_CHECK(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> g(mu);
+  cudaMemPool_t &p = pools[dev & 63];
+  if (!p) {
+    cudaMemPoolProps props = {};
+    props.allocType = cudaMemAllocationTypePinned;
+    props.handleTypes = cudaMemHandleTypeNone;
+    props.location.type = cudaMemLocationTypeDevice;
+    props.location.id = dev;
+    CB_CHECK(cudaMemPoolCreate(&p, &props));
+    unsigned long long keep = ~0ull;
+    CB_CHECK(cudaMemPoolSetAttribute(p, cudaMemPoolAttrReleaseThreshold, &keep));
+  }
+  return p;
+}
+
 void ks_imma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
                     const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
                     u32 level, u32 num_samples) {
@@ -222,8 +243,13 @@ void ks_imma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64
   chunk = std::max<u32>(imma::TM, chunk / imma::TM * imma::TM);
   unsigned char *Bt = nullptr;
   signed char *D = nullptr;
-  CB_CHECK(cudaMallocAsync((void **)&Bt, (size_t)Np * Kp, stream));
-  CB_CHECK(cudaMallocAsync((void **)&D, (size_t)chunk * Kp, stream));
+  // Scratch comes from a library-owned, stream-ordered pool that never returns memory to the
+  // driver: the default pool trims itself at every synchronisation (release threshold 0), and
+  // re-mapping ~230 MB per call costs milliseconds on one GPU and hundreds of milliseconds when
+  // 8 processes do it at once (measured: 8-GPU step 376 ms vs 236 ms on one GPU).
+  cudaMemPool_t pool = ks_scratch_pool();
+  CB_CHECK(cudaMallocFromPoolAsync((void **)&Bt, (size_t)Np * Kp, pool, stream));
+  CB_CHECK(cudaMallocFromPoolAsync((void **)&D, (size_t)chunk * Kp, pool, stream));
   {
     dim3 grid((Np / 8 + 31) / 32, Kp / 64);
     imma::ks_planes_kernel<<<grid, 256, 0, stream>>>(Bt, ksk, K, out_size, Kp, Np / 8);
