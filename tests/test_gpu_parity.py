@@ -238,6 +238,39 @@ def test_pbs_large_polynomials(engine, name, n_small, bits):
     _pbs_check(engine, keyset(name, n_override=n_small), 8, bits, use_ks=False)
 
 
+@pytest.mark.parametrize("k,N,b,l,sig_glwe", [
+    (3, 512, 18, 1, 1.1919984450689246e-23 ** 0.5),   # BOOLEAN_DEFAULT / MESSAGE_1_CARRY_1
+    (5, 256, 15, 1, 1.3996292326131784e-19 ** 0.5),   # MESSAGE_1_CARRY_0
+    (2, 512, 8, 2, 1.6434266310406663e-15 ** 0.5),    # MESSAGE_2_CARRY_0
+    (2, 1024, 23, 1, 8.645717832544903e-32 ** 0.5),   # BOOLEAN_TFHE_LIB / MESSAGE_*_CARRY_* rows
+    (1, 4096, 22, 1, 4.70197740328915e-38 ** 0.5),    # MESSAGE_5_CARRY_0
+    (1, 8192, 15, 2, 4.70197740328915e-38 ** 0.5),    # MESSAGE_3_CARRY_3
+    (4, 256, 12, 2, 2.0 ** -40), (6, 256, 10, 3, 2.0 ** -40), (3, 2048, 20, 1, 2.0 ** -60),
+])
+def test_pbs_reference_parameter_table(engine, k, N, b, l, sig_glwe):
+    """The (k, N, base_log, level) rows of the reference's own GPU test table
+    (TCB/tests_and_benchmarks/tests/test_classical_pbs.cpp:232-376) plus the remaining (k, N)
+    instantiations of the generic kernel, with the small dimension cut to 28 so that the oracle
+    finishes in seconds (the CMUX loop body does not depend on n)."""
+    prm = TfheParams(f"REF_k{k}_N{N}", 28, k, N, l, b, 3, 4, 2, 2.0 ** -24, sig_glwe)
+    _pbs_check(engine, KeySet(prm, seed=42), 9, 2, use_ks=False)
+
+
+def test_pbs_empty_batch(engine):
+    """num_samples == 0 is a no-op (no launch, output untouched), like the keyswitch."""
+    import torch
+
+    ks = keyset("TOY512")
+    p = ks.p
+    out = torch.full((3, p.big_n + 1), 5, dtype=torch.int64, device=engine.device)
+    cts = torch.zeros((3, p.n + 1), dtype=torch.int64, device=engine.device)
+    lut = engine.to_device(trivial_glwe(np.zeros(p.N, dtype=np.uint64), p.k))
+    d_fbsk = engine.convert_bsk(ks.bsk, p.n, p.k, p.l, p.N)
+    engine.bootstrap(cts, lut, None, d_fbsk, p.n, p.k, p.N, p.b, p.l, out=out, num_samples=0)
+    engine.synchronize()
+    assert bool((out == 5).all())
+
+
 def test_pbs_zero_mask_elements_and_indexes(engine):
     """Mask elements equal to 0 are skipped (bootstrap.rs:287); permuted index arrays; per-sample
     LUT indexes into a table of two accumulators."""
