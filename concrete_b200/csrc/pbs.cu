@@ -102,7 +102,7 @@ template <int K, int LOGN> struct PbsCfg {
   static constexpr int M = F::M;
   static constexpr int N = 2 * M;
   static constexpr int P = F::P;
-  static constexpr int REGS = (K == 1) ? 128 : ((K == 2) ? 168 : 128);
+  static constexpr int REGS = (K == 1) ? (LOGN == 12 ? 255 : 128) : ((K == 2) ? 255 : 128);
   static constexpr int MINB_R = (65536 / REGS) / T;
   static constexpr int MINB = MINB_R < 1 ? 1 : (MINB_R > 16 ? 16 : MINB_R);
   static constexpr size_t FBUF_BYTES = (size_t)F::BUF_ELEMS * sizeof(double2);
