@@ -279,6 +279,8 @@ pbs_kernel(const PbsArgs a) {
   }
 }
 
+#include "pbs_grp.cuh"
+
 // ------------------------------------------------------------------------------------------
 // K4: standard-domain BSK -> Fourier, in place, one CTA per polynomial.
 // Output polynomial `poly` occupies the same N*8 bytes as the input polynomial `poly`:
@@ -354,6 +356,10 @@ poly_mul_kernel(const double *in1, const double *in2, double *out,
 // ------------------------------------------------------------------------------------------
 struct Variant {
   void (*pbs)(const PbsArgs);
+  void (*pbs_grp)(const PbsArgs); // group-per-polynomial kernel (pbs_grp.cuh), if it fits
+  int grp_threads;
+  size_t grp_smem_fixed;
+  bool grp_fits;
   void (*convert)(double2 *, const double2 *, size_t);
   void (*polymul)(const double *, const double *, double *, const double2 *, u32);
   int T;
@@ -365,6 +371,10 @@ template <int K, int LOGN> Variant make_variant() {
   using C = PbsCfg<K, LOGN>;
   Variant v;
   v.pbs = pbs_kernel<K, LOGN>;
+  v.pbs_grp = pbs_kernel_grp<K, LOGN>;
+  v.grp_threads = GrpCfg<K, LOGN>::THREADS;
+  v.grp_smem_fixed = GrpCfg<K, LOGN>::SMEM_FIXED;
+  v.grp_fits = GrpCfg<K, LOGN>::FITS;
   v.convert = bsk_convert_kernel<K, LOGN>;
   v.polymul = poly_mul_kernel<K, LOGN>;
   v.T = C::T;
@@ -401,6 +411,7 @@ struct PbsBuffer {
   int gpu;
   u32 k, N, level, max_samples;
   int grid_cap;           // resident CTAs for the persistent launch
+  int grp_grid_cap;       // same for the group-per-polynomial kernel (0: not usable)
   size_t smem_fixed;      // dynamic smem without the a_hat table
   ulonglong2 *global_acc; // device scratch when the accumulator does not fit in smem
   Variant v;
@@ -440,6 +451,15 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
   if (per_sm < 1)
     CB_PANIC("Cuda error (classical PBS): kernel does not fit on an SM (smem %zu B)", smem);
   b->grid_cap = per_sm * sms;
+  b->grp_grid_cap = 0;
+  if (v.grp_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
+    const size_t gsmem = v.grp_smem_fixed + 4096;
+    int occ = 0;
+    CB_CHECK(cudaFuncSetAttribute(v.pbs_grp, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)gsmem));
+    CB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.pbs_grp, v.grp_threads, gsmem));
+    b->grp_grid_cap = occ * sms;
+  }
   if (v.acc_global && allocate) {
     size_t ctas = (size_t)std::min<u32>((u32)b->grid_cap, count ? count : 1);
     CB_CHECK(cudaMallocAsync((void **)&b->global_acc, ctas * v.acc_bytes, stream));
@@ -548,6 +568,14 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   a.lut_count = lut_count;
   a.lut_stride = lut_stride;
   a.skew_ns = 0;
+  if (b->grp_grid_cap > 0 && n <= 2048) {
+    const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
+    const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
+    v.pbs_grp<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
   const size_t smem = pbs_smem_bytes(v, n);
   CB_CHECK(cudaFuncSetAttribute(v.pbs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   v.pbs<<<grid, v.T, smem, stream>>>(a);

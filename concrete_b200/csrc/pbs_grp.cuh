@@ -1,0 +1,170 @@
+// pbs_grp.cuh — fused PBS with one THREAD GROUP per GLWE polynomial (every (k, N) whose working
+// set fits in shared memory; included by pbs.cu inside its anonymous namespace).
+//
+// Same arithmetic and the same Fourier-key layout as pbs_kernel (pbs.cu); what changes is who
+// holds what.  ncu/ptxas on pbs_kernel: every thread carries the Fourier accumulators of ALL k+1
+// output polynomials (8(k+1)P registers) next to its transform points and the decomposition
+// states, ptxas spills (P4: 236 B, P6: 472 B per thread) and the (k+1)·l forward transforms of a
+// CMUX run one after the other.  Here a CTA has k+1 groups of T = M/P threads:
+//   phase A  group r: ct1_r = ACC_r·X^a − ACC_r, rounding, digits of level m, forward transform,
+//            result F_{r,m} parked in the group's exchange buffer            (groups in parallel)
+//   phase B  group c: out_c += Σ_r F_{r,m} ⊙ GGSW[m][r][c]     (F from shared memory, key from L2)
+//   phase C  group c: inverse transform of out_c, ACC_c += round(·)          (groups in parallel)
+// so a thread holds P points + P accumulators of ONE polynomial (128 registers, no spills), the
+// k+1 transforms of a phase overlap, and occupancy is set by shared memory, not registers.
+// CTA-wide barriers: two per decomposition level; transforms use one named barrier per group.
+#pragma once
+
+template <int K, int LOGN> struct GrpCfg {
+  using C = PbsCfg<K, LOGN>;
+  static constexpr int GS = K + 1;
+  static constexpr int T = C::T;            // threads per group (same split as pbs_kernel, so the
+  static constexpr int P = C::P;            // Fourier key layout dst[p*T + t] is shared)
+  static constexpr int THREADS = GS * T;
+  static constexpr size_t SMEM_FIXED = (size_t)GS * C::FBUF_BYTES + C::ACC_BYTES;
+  static constexpr bool FITS = THREADS <= 512 && SMEM_FIXED + 4096 <= 232448; // >= 128 regs/thread
+  static constexpr int BY_SMEM = FITS ? (int)(232448 / (SMEM_FIXED + 4096)) : 1;
+  static constexpr int BY_REGS = (65536 / 128) / THREADS;  // spill-free at ~128 registers
+  static constexpr int MINB_ = BY_SMEM < BY_REGS ? BY_SMEM : BY_REGS;
+  static constexpr int MINB = MINB_ < 1 ? 1 : (MINB_ > 8 ? 8 : MINB_);
+};
+
+template <int K, int LOGN>
+__global__ void __launch_bounds__(GrpCfg<K, LOGN>::THREADS, GrpCfg<K, LOGN>::MINB)
+pbs_kernel_grp(const PbsArgs a) {
+  using C = PbsCfg<K, LOGN>;
+  using G = GrpCfg<K, LOGN>;
+  constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
+  constexpr int GS = K + 1, THREADS = G::THREADS;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  double2 *fbuf_all = reinterpret_cast<double2 *>(smem);
+  ulonglong2 *acc_all = reinterpret_cast<ulonglong2 *>(smem + (size_t)GS * C::FBUF_BYTES);
+  unsigned short *s_ahat =
+      reinterpret_cast<unsigned short *>(smem + (size_t)GS * C::FBUF_BYTES + C::ACC_BYTES);
+  const int tid = threadIdx.x;
+  const int grp = tid / T, t = tid % T; // polynomial index (row in phase A, column in B/C)
+  double2 *fbuf = fbuf_all + (size_t)grp * C::F::BUF_ELEMS;
+  ulonglong2 *acc = acc_all + (size_t)grp * M;
+  const int bar_id = 1 + grp;
+  const u32 n = a.n, base_log = a.base_log, level = a.level;
+  const u64 mask = ((u64)1 << base_log) - 1;
+  const u32 round_shift = 64 - base_log * level - 1;
+  const u32 state_shift = 64 - base_log * level;
+  const double2 *__restrict__ tw = a.tw;
+  const size_t out_size = (size_t)K * N + 1;
+
+  for (u32 sample = blockIdx.x; sample < a.num_samples; sample += gridDim.x) {
+    const u64 *lwe = a.lwe_in + a.in_idx[sample] * (u64)(n + 1);
+    for (u32 i = tid; i < n; i += THREADS)
+      s_ahat[i] = (unsigned short)modulus_switch(lwe[i], LOGN + 1);
+    const u32 b_hat = modulus_switch(lwe[n], LOGN + 1);
+    { // ACC_grp <- LUT_grp * X^(-b_hat)   (polynomial_algorithms.rs:500-539)
+      const u64 *lut = a.lut_vector + a.lut_idx[sample] * (u64)(GS * N) + (size_t)grp * N;
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        ulonglong2 v;
+        {
+          const u32 u = (j + b_hat) & (2 * N - 1);
+          const u64 w = lut[u & (N - 1)];
+          v.x = (u < (u32)N) ? w : (u64)0 - w;
+        }
+        {
+          const u32 u = (j + M + b_hat) & (2 * N - 1);
+          const u64 w = lut[u & (N - 1)];
+          v.y = (u < (u32)N) ? w : (u64)0 - w;
+        }
+        acc[j] = v;
+      }
+    }
+    __syncthreads();
+
+    for (u32 i = 0; i < n; ++i) {
+      const u32 a_hat = s_ahat[i];
+      if (a_hat == 0) continue; // uniform over the CTA (bootstrap.rs:287)
+
+      // ---- phase A (first part): rotation, rounding, decomposition state of polynomial grp
+      u64 st_re[P], st_im[P];
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        const u32 s = (u32)(j - (int)a_hat) & (2 * N - 1);
+        const u32 q = s >> LOGM;
+        const ulonglong2 src = acc[s & (M - 1)];
+        const ulonglong2 own = acc[j];
+        const u64 ra = (q & 1) ? src.y : src.x;
+        const u64 rb = (q & 1) ? src.x : src.y;
+        const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
+        const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
+        st_re[p] = closest_representable(rot_re - own.x, round_shift) >> state_shift;
+        st_im[p] = closest_representable(rot_im - own.y, round_shift) >> state_shift;
+      }
+      double2 oacc[P];
+#pragma unroll
+      for (int p = 0; p < P; ++p) oacc[p] = make_double2(0.0, 0.0);
+
+#pragma unroll 1
+      for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
+        {
+          double2 x[P];
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            x[p].x = __int2double_rn((int)(u32)decompose_one_level(st_re[p], mask, base_log));
+            x[p].y = __int2double_rn((int)(u32)decompose_one_level(st_im[p], mask, base_log));
+          }
+          cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw, bar_id);
+          cbfft::group_sync<T>(bar_id); // last exchange of the transform fully read
+#pragma unroll
+          for (int p = 0; p < P; ++p) fbuf[p * T + t] = x[p]; // F_{grp,m} in key order
+        }
+        __syncthreads(); // every F_{r,m} is visible
+        // ---- phase B: column grp of the external product
+        const double2 *__restrict__ g =
+            a.bsk + (((size_t)i * level + m) * GS * GS + grp) * M + t;
+#pragma unroll
+        for (int r = 0; r < GS; ++r) {
+          const double2 *fr = fbuf_all + (size_t)r * C::F::BUF_ELEMS + t;
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            const double2 w = __ldg(&g[(size_t)r * GS * M + p * T]);
+            const double2 f = fr[p * T];
+            oacc[p].x = fma(f.x, w.x, fma(-f.y, w.y, oacc[p].x));
+            oacc[p].y = fma(f.x, w.y, fma(f.y, w.x, oacc[p].y));
+          }
+        }
+        __syncthreads(); // all reads of the F buffers done before they are reused
+      }
+
+      // ---- phase C: inverse transform of column grp, torus rounding, accumulate
+      cbfft::inverse<LOGM, LOGP>(oacc, fbuf, t, tw, bar_id);
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        ulonglong2 v = acc[j];
+        v.x += from_torus(oacc[p].x);
+        v.y += from_torus(oacc[p].y);
+        acc[j] = v;
+      }
+      cbfft::group_sync<T>(bar_id); // ACC_grp complete before its rotated reads of the next CMUX
+    }
+    __syncthreads();
+
+    // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride
+    for (u32 li = 0; li < a.lut_count; ++li) {
+      const u32 nth = li * a.lut_stride;
+      u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
+      for (int x = tid; x < K * N; x += THREADS) {
+        const int c = x >> LOGN, j = x & (N - 1);
+        const int src = (j <= (int)nth) ? ((int)nth - j) : (N + (int)nth - j);
+        const ulonglong2 pr = acc_all[c * M + (src & (M - 1))];
+        const u64 v = (src < M) ? pr.x : pr.y;
+        out[x] = (j <= (int)nth) ? v : (u64)0 - v;
+      }
+      if (tid == 0) {
+        const ulonglong2 pr = acc_all[K * M + (nth & (M - 1))];
+        out[(size_t)K * N] = (nth < (u32)M) ? pr.x : pr.y;
+      }
+    }
+    __syncthreads();
+  }
+}
