@@ -74,13 +74,21 @@ __device__ __forceinline__ void fwd_stages(double2 (&x)[1 << LOGP], int t, int l
   for (int s = s_begin; s < s_end; ++s) {
     const int beta = LOGM - 1 - s; // index bit paired by this stage
     const int rho = beta - lo;     // in-thread bit
+    // in-thread slots r and r | 2^(rho+1) sit in blocks b (even) and b + 1, and
+    // tw[2^s + b + 1] = i * tw[2^s + b]: one load serves both (the twiddle loads are a third of
+    // the L1 traffic of the fused PBS kernels, profiles/r1_grp_p4_ncu.txt)
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
+      if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
       const int idx = elem_index<LOGP>(t, r, lo);
       const int b = idx >> (beta + 1);
       const double2 w = __ldg(&tw[(1 << s) + b]);
       bfly_ct(x[r], x[r | (1 << rho)], w);
+      if (rho + 1 < LOGP) {
+        const int r2 = r | (1 << (rho + 1));
+        bfly_ct(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
+      }
     }
   }
 }
@@ -97,10 +105,15 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[1 << LOGP], int t, int l
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
+      if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
       const int idx = elem_index<LOGP>(t, r, lo);
       const int b = idx >> (beta + 1);
       const double2 w = __ldg(&tw[(1 << s) + b]);
       bfly_gs(x[r], x[r | (1 << rho)], w);
+      if (rho + 1 < LOGP) {
+        const int r2 = r | (1 << (rho + 1));
+        bfly_gs(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
+      }
     }
   }
 }
