@@ -24,6 +24,12 @@
 
 namespace cbfft {
 
+// tw[2^s + b] does not depend on M, so one small table serves every transform size: the first
+// pass of every transform pairs the top index bits, its block index b is a compile-time constant
+// (t >> lo == 0) and the twiddle becomes a constant-bank operand of the FMA (no load at all).
+constexpr int CONST_TW = 256; // stages s < 8
+__constant__ double2 c_twg[CONST_TW];
+
 template <int LOGM, int LOGP> struct Cfg {
   static constexpr int M = 1 << LOGM;
   static constexpr int P = 1 << LOGP;
@@ -82,8 +88,9 @@ __device__ __forceinline__ void fwd_stages(double2 (&x)[1 << LOGP], int t, int l
       if (r & (1 << rho)) continue;
       if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
       const int idx = elem_index<LOGP>(t, r, lo);
-      const int b = idx >> (beta + 1);
-      const double2 w = __ldg(&tw[(1 << s) + b]);
+      const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < CONST_TW);
+      const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
+      const double2 w = first_pass ? c_twg[(1 << s) + b] : __ldg(&tw[(1 << s) + b]);
       bfly_ct(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));
@@ -107,8 +114,9 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[1 << LOGP], int t, int l
       if (r & (1 << rho)) continue;
       if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
       const int idx = elem_index<LOGP>(t, r, lo);
-      const int b = idx >> (beta + 1);
-      const double2 w = __ldg(&tw[(1 << s) + b]);
+      const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < CONST_TW);
+      const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
+      const double2 w = first_pass ? c_twg[(1 << s) + b] : __ldg(&tw[(1 << s) + b]);
       bfly_gs(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));

@@ -58,6 +58,14 @@ const double2 *get_twiddles(int gpu, int logm) {
   CB_CHECK(cudaMalloc(&d, M * sizeof(double2)));
   CB_CHECK(cudaMemcpy(d, h.data(), M * sizeof(double2), cudaMemcpyHostToDevice));
   if (logm == 10) cb_w32_set_const_twiddles(h.data()); // current device == gpu
+  { // generic constant table: entries [0, min(M, 256)) are the same for every size
+    static std::map<int, size_t> filled; // per device: how many entries are valid
+    const size_t want = std::min<size_t>(M, (size_t)cbfft::CONST_TW);
+    if (filled[gpu] < want) {
+      CB_CHECK(cudaMemcpyToSymbol(cbfft::c_twg, h.data(), want * sizeof(double2)));
+      filled[gpu] = want;
+    }
+  }
   g_tw_cache[key] = d;
   return d;
 }
