@@ -20,6 +20,7 @@
 #include "fft.cuh"
 #include "../../include/concrete_b200.h"
 #include <cmath>
+#include <cooperative_groups.h>
 #include <map>
 #include <mutex>
 #include <vector>
@@ -368,6 +369,9 @@ struct Variant {
   int grp_threads;
   size_t grp_smem_fixed;
   bool grp_fits;
+  void (*pbs_grp_cl)(const PbsArgs); // cluster variant: one CTA per polynomial
+  size_t cl_smem_fixed;
+  bool cl_fits;
   void (*convert)(double2 *, const double2 *, size_t);
   void (*polymul)(const double *, const double *, double *, const double2 *, u32);
   int T;
@@ -383,6 +387,9 @@ template <int K, int LOGN> Variant make_variant() {
   v.grp_threads = GrpCfg<K, LOGN>::THREADS;
   v.grp_smem_fixed = GrpCfg<K, LOGN>::SMEM_FIXED;
   v.grp_fits = GrpCfg<K, LOGN>::FITS;
+  v.pbs_grp_cl = pbs_kernel_grp_cluster<K, LOGN>;
+  v.cl_smem_fixed = GrpCfg<K, LOGN>::CL_SMEM_FIXED;
+  v.cl_fits = GrpCfg<K, LOGN>::CL_FITS;
   v.convert = bsk_convert_kernel<K, LOGN>;
   v.polymul = poly_mul_kernel<K, LOGN>;
   v.T = C::T;
@@ -420,6 +427,7 @@ struct PbsBuffer {
   u32 k, N, level, max_samples;
   int grid_cap;           // resident CTAs for the persistent launch
   int grp_grid_cap;       // same for the group-per-polynomial kernel (0: not usable)
+  int cl_cluster_cap;     // resident clusters of the cluster variant (0: not usable)
   size_t smem_fixed;      // dynamic smem without the a_hat table
   ulonglong2 *global_acc; // device scratch when the accumulator does not fit in smem
   Variant v;
@@ -467,6 +475,28 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
                                   (int)gsmem));
     CB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.pbs_grp, v.grp_threads, gsmem));
     b->grp_grid_cap = occ * sms;
+  }
+  b->cl_cluster_cap = 0;
+  if (v.cl_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
+    const size_t csmem = v.cl_smem_fixed + 4096;
+    CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)csmem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((k + 1) * (u32)sms, 1, 1);
+    cfg.blockDim = dim3((u32)v.T, 1, 1);
+    cfg.dynamicSmemBytes = csmem;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = k + 1;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    int clusters = 0;
+    if (cudaOccupancyMaxActiveClusters(&clusters, v.pbs_grp_cl, &cfg) == cudaSuccess)
+      b->cl_cluster_cap = clusters;
+    else
+      (void)cudaGetLastError();
   }
   if (v.acc_global && allocate) {
     size_t ctas = (size_t)std::min<u32>((u32)b->grid_cap, count ? count : 1);
@@ -576,11 +606,33 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   a.lut_count = lut_count;
   a.lut_stride = lut_stride;
   a.skew_ns = 0;
-  if (b->grp_grid_cap > 0 && n <= 2048) {
+  // The cluster variant (one CTA per polynomial, F through DSMEM) is bit-compatible and fits
+  // N = 8192, but measured slower than the first kernel there (P7: 671 vs 633 ms: two cluster
+  // barriers per CMUX with one CTA per SM); it stays selectable for experiments and tests.
+  const bool force_cluster = std::getenv("CONCRETE_B200_FORCE_CLUSTER") != nullptr;
+  if (b->grp_grid_cap > 0 && n <= 2048 && !(force_cluster && b->cl_cluster_cap > 0)) {
     const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
     v.pbs_grp<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
     CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
+  if (force_cluster && b->cl_cluster_cap > 0 && n <= 2048) {
+    const u32 clusters = std::min<u32>((u32)b->cl_cluster_cap, num_samples);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(clusters * (k + 1), 1, 1);
+    cfg.blockDim = dim3((u32)v.T, 1, 1);
+    cfg.dynamicSmemBytes = v.cl_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = k + 1;
+    attr.val.clusterDim.y = 1;
+    attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    CB_CHECK(cudaLaunchKernelEx(&cfg, v.pbs_grp_cl, a));
     CB_LAUNCHED();
     return;
   }

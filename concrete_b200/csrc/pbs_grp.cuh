@@ -13,7 +13,13 @@
 // so a thread holds P points + P accumulators of ONE polynomial (128 registers, no spills), the
 // k+1 transforms of a phase overlap, and occupancy is set by shared memory, not registers.
 // CTA-wide barriers: two per decomposition level; transforms use one named barrier per group.
+//
+// CLUSTER variant (same body): when k+1 exchange buffers + the accumulator exceed one SM's shared
+// memory (N = 8192), the k+1 groups become the k+1 CTAs of a thread-block cluster, each holding
+// ONE polynomial's accumulator and exchange buffer; phase B reads the partners' F_{r,m} through
+// distributed shared memory and the CTA-wide barriers become cluster barriers.
 #pragma once
+// (pbs.cu includes <cooperative_groups.h> at file scope: this header sits in its namespace)
 
 template <int K, int LOGN> struct GrpCfg {
   using C = PbsCfg<K, LOGN>;
@@ -27,25 +33,48 @@ template <int K, int LOGN> struct GrpCfg {
   static constexpr int BY_REGS = (65536 / 128) / THREADS;  // spill-free at ~128 registers
   static constexpr int MINB_ = BY_SMEM < BY_REGS ? BY_SMEM : BY_REGS;
   static constexpr int MINB = MINB_ < 1 ? 1 : (MINB_ > 8 ? 8 : MINB_);
+  // cluster variant: one CTA per polynomial
+  static constexpr size_t CL_SMEM_FIXED = C::FBUF_BYTES + C::ACC_BYTES / GS;
+  static constexpr bool CL_FITS = T <= 512 && GS <= 8 && CL_SMEM_FIXED + 4096 <= 232448;
+  static constexpr int CL_MINB_ = (int)(232448 / (CL_SMEM_FIXED + 4096)) < (65536 / 128) / T
+                                      ? (int)(232448 / (CL_SMEM_FIXED + 4096))
+                                      : (65536 / 128) / T;
+  static constexpr int CL_MINB = CL_MINB_ < 1 ? 1 : CL_MINB_;
 };
 
-template <int K, int LOGN>
-__global__ void __launch_bounds__(GrpCfg<K, LOGN>::THREADS, GrpCfg<K, LOGN>::MINB)
-pbs_kernel_grp(const PbsArgs a) {
+template <int K, int LOGN, bool CLUSTER>
+__device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
+  namespace cg = cooperative_groups;
   using C = PbsCfg<K, LOGN>;
   using G = GrpCfg<K, LOGN>;
   constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
-  constexpr int GS = K + 1, THREADS = G::THREADS;
+  constexpr int GS = K + 1, THREADS = CLUSTER ? T : G::THREADS;
   extern __shared__ __align__(1024) unsigned char smem[];
-  double2 *fbuf_all = reinterpret_cast<double2 *>(smem);
-  ulonglong2 *acc_all = reinterpret_cast<ulonglong2 *>(smem + (size_t)GS * C::FBUF_BYTES);
-  unsigned short *s_ahat =
-      reinterpret_cast<unsigned short *>(smem + (size_t)GS * C::FBUF_BYTES + C::ACC_BYTES);
   const int tid = threadIdx.x;
-  const int grp = tid / T, t = tid % T; // polynomial index (row in phase A, column in B/C)
-  double2 *fbuf = fbuf_all + (size_t)grp * C::F::BUF_ELEMS;
-  ulonglong2 *acc = acc_all + (size_t)grp * M;
-  const int bar_id = 1 + grp;
+  // polynomial index (row in phase A, column in B/C) and index inside the group
+  const int grp = CLUSTER ? (int)cg::this_cluster().block_rank() : tid / T;
+  const int t = CLUSTER ? tid : tid % T;
+  // shared-memory map: CTA mode [GS exchange buffers][GS accumulators][a_hat];
+  //                    cluster mode [1 exchange buffer][1 accumulator][a_hat] per CTA
+  double2 *fbuf = reinterpret_cast<double2 *>(smem) + (CLUSTER ? 0 : (size_t)grp * C::F::BUF_ELEMS);
+  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (CLUSTER ? 1 : GS) * C::FBUF_BYTES) +
+                    (CLUSTER ? 0 : (size_t)grp * M);
+  unsigned short *s_ahat = reinterpret_cast<unsigned short *>(
+      smem + (CLUSTER ? C::FBUF_BYTES + C::ACC_BYTES / GS : GS * C::FBUF_BYTES + C::ACC_BYTES));
+  const double2 *fsrc[GS]; // where phase B finds F_{r,m} (own SM or a partner's, through DSMEM)
+#pragma unroll
+  for (int r = 0; r < GS; ++r) {
+    if (CLUSTER)
+      fsrc[r] = cg::this_cluster().map_shared_rank(reinterpret_cast<double2 *>(smem), r) + t;
+    else
+      fsrc[r] = reinterpret_cast<double2 *>(smem) + (size_t)r * C::F::BUF_ELEMS + t;
+  }
+  auto sync_all = [&]() {
+    if (CLUSTER) cg::this_cluster().sync(); else __syncthreads();
+  };
+  const u32 first_sample = CLUSTER ? blockIdx.x / GS : blockIdx.x;
+  const u32 sample_stride = CLUSTER ? gridDim.x / GS : gridDim.x;
+  const int bar_id = CLUSTER ? 1 : 1 + grp;
   const u32 n = a.n, base_log = a.base_log, level = a.level;
   const u64 mask = ((u64)1 << base_log) - 1;
   const u32 round_shift = 64 - base_log * level - 1;
@@ -53,7 +82,7 @@ pbs_kernel_grp(const PbsArgs a) {
   const double2 *__restrict__ tw = a.tw;
   const size_t out_size = (size_t)K * N + 1;
 
-  for (u32 sample = blockIdx.x; sample < a.num_samples; sample += gridDim.x) {
+  for (u32 sample = first_sample; sample < a.num_samples; sample += sample_stride) {
     const u64 *lwe = a.lwe_in + a.in_idx[sample] * (u64)(n + 1);
     for (u32 i = tid; i < n; i += THREADS)
       s_ahat[i] = (unsigned short)modulus_switch(lwe[i], LOGN + 1);
@@ -77,7 +106,7 @@ pbs_kernel_grp(const PbsArgs a) {
         acc[j] = v;
       }
     }
-    __syncthreads();
+    sync_all();
 
     for (u32 i = 0; i < n; ++i) {
       const u32 a_hat = s_ahat[i];
@@ -117,13 +146,28 @@ pbs_kernel_grp(const PbsArgs a) {
 #pragma unroll
           for (int p = 0; p < P; ++p) fbuf[p * T + t] = x[p]; // F_{grp,m} in key order
         }
-        __syncthreads(); // every F_{r,m} is visible
-        // ---- phase B: column grp of the external product
         const double2 *__restrict__ g =
             a.bsk + (((size_t)i * level + m) * GS * GS + grp) * M + t;
+        // ---- phase B: column grp of the external product.  The own term (r = grp) reads
+        // back exactly what this thread stored, so in cluster mode it runs between the arrive
+        // and the wait of the cluster barrier and covers the barrier's latency.
+        if (CLUSTER) {
+          asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            const double2 w = __ldg(&g[(size_t)grp * GS * M + p * T]);
+            const double2 f = fbuf[p * T + t];
+            oacc[p].x = fma(f.x, w.x, fma(-f.y, w.y, oacc[p].x));
+            oacc[p].y = fma(f.x, w.y, fma(f.y, w.x, oacc[p].y));
+          }
+          asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+        } else {
+          sync_all(); // every F_{r,m} is visible
+        }
 #pragma unroll
         for (int r = 0; r < GS; ++r) {
-          const double2 *fr = fbuf_all + (size_t)r * C::F::BUF_ELEMS + t;
+          if (CLUSTER && r == grp) continue; // done above
+          const double2 *fr = fsrc[r];
 #pragma unroll
           for (int p = 0; p < P; ++p) {
             const double2 w = __ldg(&g[(size_t)r * GS * M + p * T]);
@@ -132,7 +176,7 @@ pbs_kernel_grp(const PbsArgs a) {
             oacc[p].y = fma(f.x, w.y, fma(f.y, w.x, oacc[p].y));
           }
         }
-        __syncthreads(); // all reads of the F buffers done before they are reused
+        sync_all(); // all reads of the F buffers done before they are reused
       }
 
       // ---- phase C: inverse transform of column grp, torus rounding, accumulate
@@ -147,24 +191,37 @@ pbs_kernel_grp(const PbsArgs a) {
       }
       cbfft::group_sync<T>(bar_id); // ACC_grp complete before its rotated reads of the next CMUX
     }
-    __syncthreads();
 
-    // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride
+    // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride: group c < k
+    // writes mask polynomial c from its own accumulator, group k the body
     for (u32 li = 0; li < a.lut_count; ++li) {
       const u32 nth = li * a.lut_stride;
       u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
-      for (int x = tid; x < K * N; x += THREADS) {
-        const int c = x >> LOGN, j = x & (N - 1);
-        const int src = (j <= (int)nth) ? ((int)nth - j) : (N + (int)nth - j);
-        const ulonglong2 pr = acc_all[c * M + (src & (M - 1))];
-        const u64 v = (src < M) ? pr.x : pr.y;
-        out[x] = (j <= (int)nth) ? v : (u64)0 - v;
-      }
-      if (tid == 0) {
-        const ulonglong2 pr = acc_all[K * M + (nth & (M - 1))];
+      if (grp < K) {
+        for (int j = t; j < N; j += T) {
+          const int src = (j <= (int)nth) ? ((int)nth - j) : (N + (int)nth - j);
+          const ulonglong2 pr = acc[src & (M - 1)];
+          const u64 v = (src < M) ? pr.x : pr.y;
+          out[(size_t)grp * N + j] = (j <= (int)nth) ? v : (u64)0 - v;
+        }
+      } else if (t == 0) {
+        const ulonglong2 pr = acc[nth & (M - 1)];
         out[(size_t)K * N] = (nth < (u32)M) ? pr.x : pr.y;
       }
     }
-    __syncthreads();
+    sync_all(); // a_hat table and buffers are reused by the next sample
   }
+}
+
+template <int K, int LOGN>
+__global__ void __launch_bounds__(GrpCfg<K, LOGN>::THREADS, GrpCfg<K, LOGN>::MINB)
+pbs_kernel_grp(const PbsArgs a) {
+  pbs_grp_body<K, LOGN, false>(a);
+}
+
+// launched with cluster dimension (k+1, 1, 1): CTA rank in the cluster = polynomial index
+template <int K, int LOGN>
+__global__ void __launch_bounds__(PbsCfg<K, LOGN>::T, GrpCfg<K, LOGN>::CL_MINB)
+pbs_kernel_grp_cluster(const PbsArgs a) {
+  pbs_grp_body<K, LOGN, true>(a);
 }

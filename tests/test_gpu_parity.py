@@ -256,6 +256,15 @@ def test_pbs_reference_parameter_table(engine, k, N, b, l, sig_glwe):
     _pbs_check(engine, KeySet(prm, seed=42), 9, 2, use_ks=False)
 
 
+@pytest.mark.parametrize("name,n_small", [("TOY512", None), ("P4", 24), ("P7", 16)])
+def test_pbs_cluster_variant(engine, name, n_small, monkeypatch):
+    """The thread-block-cluster variant of the group kernel (one CTA per GLWE polynomial, Fourier
+    digits exchanged through distributed shared memory; pbs_grp.cuh) is not the default anywhere
+    (measured slower at N = 8192) but must stay correct: same checks as the default path."""
+    monkeypatch.setenv("CONCRETE_B200_FORCE_CLUSTER", "1")
+    _pbs_check(engine, keyset(name, n_override=n_small), 7, 3, use_ks=False)
+
+
 def test_pbs_empty_batch(engine):
     """num_samples == 0 is a no-op (no launch, output untouched), like the keyswitch."""
     import torch
