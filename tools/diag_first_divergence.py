@@ -1,7 +1,9 @@
 """Diagnostic: find the first CMUX iteration where GPU and oracle PBS diverge."""
 import sys
 import numpy as np, torch
-sys.path.insert(0, "tests")
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 from harness import *
 from concrete_b200 import Engine, as_u64
 

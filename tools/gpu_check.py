@@ -1,7 +1,9 @@
-"""Quick manual GPU check (development aid): python scripts_gpu_check.py [param names]."""
+"""Quick manual GPU check (development aid): python tools/gpu_check.py [param names]."""
 import sys, time
 import numpy as np, torch
-sys.path.insert(0, "tests")
+import os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
 from harness import *
 from concrete_b200 import Engine, as_i64, as_u64
 

@@ -1,4 +1,4 @@
-"""Stall samples per code segment from an .ncu-rep source page: python scripts_ncu_source.py rep [seg]"""
+"""Stall samples per code segment from an .ncu-rep source page: python tools/ncu_source.py rep [seg]"""
 import csv, subprocess, sys
 rep = sys.argv[1]; seg = int(sys.argv[2]) if len(sys.argv) > 2 else 400
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout

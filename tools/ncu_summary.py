@@ -1,4 +1,4 @@
-"""Summarise one kernel of an .ncu-rep (run here, no GPU): python scripts_ncu_summary.py rep [idx]"""
+"""Summarise one kernel of an .ncu-rep (run here, no GPU): python tools/ncu_summary.py rep [idx]"""
 import csv, subprocess, sys
 rep = sys.argv[1]; idx = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout

@@ -1,3 +1,4 @@
+cd "$(dirname "$0")/.." && true
 run() { env "$@" timeout 300 python bench.py --steps 2 --warmup 1 --samples ${SAMPLES:-7104} --no-cpu-baseline --no-e2e --no-ref-gpu 2>&1 | python -c "
 import sys,json
 tag=' '.join(sys.argv[1:])
