@@ -217,3 +217,29 @@ def test_wrappers_sharded_over_two_gpus(engine):
     rt.batched_mapped_bootstrap(out, ref_mid, tlus, p.n, p.N, p.l, p.b, p.k, bi)
     assert np.array_equal(ks.decrypt_big(out, bits), tables[np.arange(num), msgs])
     rt.close()
+
+
+@pytest.mark.parametrize("name,num,bits", [("P7", 1024, 6), ("P8", 512, 7), ("P6", 2048, 5)])
+def test_cfg3_large_polynomial_full_size(engine, name, num, bits):
+    """configs[2]: full parameter sets with N = 4096 / 8192 / 16384 (all n CMUX iterations, real
+    noise, one bit of margin below the precision the set was optimised for) — too large for the
+    oracle, so the checks are size-independent: every decryption equals LUT[m] after
+    keyswitch + PBS, and a spot sample of keyswitch outputs matches the oracle word for word."""
+    from concrete_b200 import as_u64
+
+    p = PARAMS[name]
+    ks = KeySet(p, seed=42, fourier_oracle=False)
+    rng = np.random.default_rng(31)
+    msgs = rng.integers(0, 1 << bits, num).astype(np.uint64)
+    table = ((np.arange(1 << bits) * 3 + 1) % (1 << bits)).astype(np.uint64)
+    lut = trivial_glwe(expand_lut(table, p.N, bits), p.k)
+    cts = ks.encrypt_big(msgs, bits, seed=5)
+    d_mid = engine.keyswitch(engine.to_device(cts), engine.upload_ksk(ks.ksk), p.big_n, p.n,
+                             p.b_ks, p.l_ks)
+    d_fbsk = engine.convert_bsk(ks.bsk, p.n, p.k, p.l, p.N)
+    d_out = engine.bootstrap(d_mid, engine.to_device(lut), None, d_fbsk, p.n, p.k, p.N, p.b, p.l)
+    engine.synchronize()
+    assert np.array_equal(ks.decrypt_big(as_u64(d_out), bits), table[msgs])
+    pick = rng.choice(num, 8, replace=False)
+    ref_mid = orc.keyswitch(np.ascontiguousarray(cts[pick]), ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    assert np.array_equal(as_u64(d_mid)[pick], ref_mid)
