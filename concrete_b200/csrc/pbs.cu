@@ -103,7 +103,8 @@ __device__ __forceinline__ u64 from_torus(double x) {
 template <int K, int LOGN> struct PbsCfg {
   static constexpr int LOGM = LOGN - 1;
   // points per thread: keep (K+1)*P*2 doubles of Fourier accumulators in registers
-  static constexpr int LOGP_WANT = (K <= 2) ? 3 : (K <= 5 ? 2 : 1);
+  // N = 16384: 16 points per thread (T = 512, 128 registers) for the cluster kernel of pbs_grp.cuh
+  static constexpr int LOGP_WANT = (K == 1 && LOGN == 14) ? 4 : ((K <= 2) ? 3 : (K <= 5 ? 2 : 1));
   static constexpr int LOGP_MIN = (LOGM - LOGP_WANT > 10) ? (LOGM - 10) : LOGP_WANT; // T <= 1024
   static constexpr int LOGP = (LOGM - LOGP_MIN < 5) ? (LOGM - 5) : LOGP_MIN;         // T >= 32
   using F = cbfft::Cfg<LOGM, LOGP>;
@@ -609,7 +610,12 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   // The cluster variant (one CTA per polynomial, F through DSMEM) is bit-compatible and fits
   // N = 8192, but measured slower than the first kernel there (P7: 671 vs 633 ms: two cluster
   // barriers per CMUX with one CTA per SM); it stays selectable for experiments and tests.
-  const bool force_cluster = std::getenv("CONCRETE_B200_FORCE_CLUSTER") != nullptr;
+  // Exception: when the accumulator lives in global memory anyway (N = 16384) the cluster
+  // variant is the default: one polynomial per CTA keeps 16 points per thread in 128 registers
+  // where the first kernel is capped at 64 registers with 2 KB of spills per thread.
+  const bool force_cluster =
+      std::getenv("CONCRETE_B200_FORCE_CLUSTER") != nullptr ||
+      (v.acc_global && b->global_acc && !std::getenv("CONCRETE_B200_NO_CLUSTER"));
   if (b->grp_grid_cap > 0 && n <= 2048 && !(force_cluster && b->cl_cluster_cap > 0)) {
     const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
@@ -619,7 +625,9 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     return;
   }
   if (force_cluster && b->cl_cluster_cap > 0 && n <= 2048) {
-    const u32 clusters = std::min<u32>((u32)b->cl_cluster_cap, num_samples);
+    u32 clusters = std::min<u32>((u32)b->cl_cluster_cap, num_samples);
+    if (v.acc_global) // one accumulator slot per cluster in the scratch buffer
+      clusters = std::min<u32>(clusters, std::max<u32>(1, std::min<u32>((u32)b->grid_cap, b->max_samples)));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(clusters * (k + 1), 1, 1);
     cfg.blockDim = dim3((u32)v.T, 1, 1);

@@ -34,7 +34,7 @@ template <int K, int LOGN> struct GrpCfg {
   static constexpr int MINB_ = BY_SMEM < BY_REGS ? BY_SMEM : BY_REGS;
   static constexpr int MINB = MINB_ < 1 ? 1 : (MINB_ > 8 ? 8 : MINB_);
   // cluster variant: one CTA per polynomial
-  static constexpr size_t CL_SMEM_FIXED = C::FBUF_BYTES + C::ACC_BYTES / GS;
+  static constexpr size_t CL_SMEM_FIXED = C::FBUF_BYTES + (C::ACC_GLOBAL ? 0 : C::ACC_BYTES / GS);
   static constexpr bool CL_FITS = T <= 512 && GS <= 8 && CL_SMEM_FIXED + 4096 <= 232448;
   static constexpr int CL_MINB_ = (int)(232448 / (CL_SMEM_FIXED + 4096)) < (65536 / 128) / T
                                       ? (int)(232448 / (CL_SMEM_FIXED + 4096))
@@ -57,10 +57,14 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   // shared-memory map: CTA mode [GS exchange buffers][GS accumulators][a_hat];
   //                    cluster mode [1 exchange buffer][1 accumulator][a_hat] per CTA
   double2 *fbuf = reinterpret_cast<double2 *>(smem) + (CLUSTER ? 0 : (size_t)grp * C::F::BUF_ELEMS);
-  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (CLUSTER ? 1 : GS) * C::FBUF_BYTES) +
-                    (CLUSTER ? 0 : (size_t)grp * M);
+  // (N = 16384 in cluster mode: the accumulator of this CTA's polynomial lives in global memory)
+  constexpr bool ACC_G = CLUSTER && C::ACC_GLOBAL;
+  ulonglong2 *acc =
+      ACC_G ? a.global_acc + (size_t)blockIdx.x * M
+            : reinterpret_cast<ulonglong2 *>(smem + (CLUSTER ? 1 : GS) * C::FBUF_BYTES) +
+                  (CLUSTER ? 0 : (size_t)grp * M);
   unsigned short *s_ahat = reinterpret_cast<unsigned short *>(
-      smem + (CLUSTER ? C::FBUF_BYTES + C::ACC_BYTES / GS : GS * C::FBUF_BYTES + C::ACC_BYTES));
+      smem + (CLUSTER ? G::CL_SMEM_FIXED : GS * C::FBUF_BYTES + C::ACC_BYTES));
   const double2 *fsrc[GS]; // where phase B finds F_{r,m} (own SM or a partner's, through DSMEM)
 #pragma unroll
   for (int r = 0; r < GS; ++r) {
