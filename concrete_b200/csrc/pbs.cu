@@ -20,6 +20,7 @@
 #include "fft.cuh"
 #include "../../include/concrete_b200.h"
 #include <cmath>
+#include <type_traits>
 #include <cooperative_groups.h>
 #include <map>
 #include <mutex>
@@ -367,6 +368,8 @@ poly_mul_kernel(const double *in1, const double *in2, double *out,
 struct Variant {
   void (*pbs)(const PbsArgs);
   void (*pbs_grp)(const PbsArgs); // group-per-polynomial kernel (pbs_grp.cuh), if it fits
+  void (*pbs_grp_w)(const PbsArgs);    // same with 64-bit decomposition states (b*l > 31)
+  void (*pbs_grp_cl_w)(const PbsArgs);
   int grp_threads;
   size_t grp_smem_fixed;
   bool grp_fits;
@@ -384,11 +387,13 @@ template <int K, int LOGN> Variant make_variant() {
   using C = PbsCfg<K, LOGN>;
   Variant v;
   v.pbs = pbs_kernel<K, LOGN>;
-  v.pbs_grp = pbs_kernel_grp<K, LOGN>;
+  v.pbs_grp = pbs_kernel_grp<K, LOGN, true>;
+  v.pbs_grp_w = pbs_kernel_grp<K, LOGN, false>;
+  v.pbs_grp_cl_w = pbs_kernel_grp_cluster<K, LOGN, false>;
   v.grp_threads = GrpCfg<K, LOGN>::THREADS;
   v.grp_smem_fixed = GrpCfg<K, LOGN>::SMEM_FIXED;
   v.grp_fits = GrpCfg<K, LOGN>::FITS;
-  v.pbs_grp_cl = pbs_kernel_grp_cluster<K, LOGN>;
+  v.pbs_grp_cl = pbs_kernel_grp_cluster<K, LOGN, true>;
   v.cl_smem_fixed = GrpCfg<K, LOGN>::CL_SMEM_FIXED;
   v.cl_fits = GrpCfg<K, LOGN>::CL_FITS;
   v.convert = bsk_convert_kernel<K, LOGN>;
@@ -474,6 +479,8 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
     int occ = 0;
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)gsmem));
+    CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_w, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)gsmem));
     CB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.pbs_grp, v.grp_threads, gsmem));
     b->grp_grid_cap = occ * sms;
   }
@@ -481,6 +488,8 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
   if (v.cl_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
     const size_t csmem = v.cl_smem_fixed + 4096;
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)csmem));
+    CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl_w, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)csmem));
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((k + 1) * (u32)sms, 1, 1);
@@ -619,7 +628,7 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   if (b->grp_grid_cap > 0 && n <= 2048 && !(force_cluster && b->cl_cluster_cap > 0)) {
     const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
-    v.pbs_grp<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
+    (base_log * level <= 31 ? v.pbs_grp : v.pbs_grp_w)<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
     return;
@@ -640,7 +649,7 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     attr.val.clusterDim.z = 1;
     cfg.attrs = &attr;
     cfg.numAttrs = 1;
-    CB_CHECK(cudaLaunchKernelEx(&cfg, v.pbs_grp_cl, a));
+    CB_CHECK(cudaLaunchKernelEx(&cfg, base_log * level <= 31 ? v.pbs_grp_cl : v.pbs_grp_cl_w, a));
     CB_LAUNCHED();
     return;
   }

@@ -42,8 +42,21 @@ template <int K, int LOGN> struct GrpCfg {
   static constexpr int CL_MINB = CL_MINB_ < 1 ? 1 : CL_MINB_;
 };
 
-template <int K, int LOGN, bool CLUSTER>
+// signed digit of one level on a state of type S (iter.rs:121-133).  S = u32 is exact whenever
+// base_log * level <= 31 (the state has base_log * level bits) and halves the registers the
+// decomposition states hold across the transforms of a multi-level CMUX.
+template <class S> __device__ __forceinline__ S grp_decompose(S &state, S mask, u32 base_log) {
+  S res = state & mask;
+  state >>= base_log;
+  S carry = ((res - 1) | state) & res;
+  carry >>= (base_log - 1);
+  state += carry;
+  return res - (carry << base_log);
+}
+
+template <int K, int LOGN, bool CLUSTER, bool NARROW>
 __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
+  using st_t = typename std::conditional<NARROW, u32, u64>::type;
   namespace cg = cooperative_groups;
   using C = PbsCfg<K, LOGN>;
   using G = GrpCfg<K, LOGN>;
@@ -80,7 +93,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   const u32 sample_stride = CLUSTER ? gridDim.x / GS : gridDim.x;
   const int bar_id = CLUSTER ? 1 : 1 + grp;
   const u32 n = a.n, base_log = a.base_log, level = a.level;
-  const u64 mask = ((u64)1 << base_log) - 1;
+  const st_t mask = (st_t)(((u64)1 << base_log) - 1);
   const u32 round_shift = 64 - base_log * level - 1;
   const u32 state_shift = 64 - base_log * level;
   const double2 *__restrict__ tw = a.tw;
@@ -117,7 +130,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
       if (a_hat == 0) continue; // uniform over the CTA (bootstrap.rs:287)
 
       // ---- phase A (first part): rotation, rounding, decomposition state of polynomial grp
-      u64 st_re[P], st_im[P];
+      st_t st_re[P], st_im[P];
 #pragma unroll
       for (int p = 0; p < P; ++p) {
         const int j = t + p * T;
@@ -129,8 +142,8 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
         const u64 rb = (q & 1) ? src.x : src.y;
         const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
         const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
-        st_re[p] = closest_representable(rot_re - own.x, round_shift) >> state_shift;
-        st_im[p] = closest_representable(rot_im - own.y, round_shift) >> state_shift;
+        st_re[p] = (st_t)(closest_representable(rot_re - own.x, round_shift) >> state_shift);
+        st_im[p] = (st_t)(closest_representable(rot_im - own.y, round_shift) >> state_shift);
       }
       double2 oacc[P];
 #pragma unroll
@@ -142,8 +155,8 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           double2 x[P];
 #pragma unroll
           for (int p = 0; p < P; ++p) {
-            x[p].x = __int2double_rn((int)(u32)decompose_one_level(st_re[p], mask, base_log));
-            x[p].y = __int2double_rn((int)(u32)decompose_one_level(st_im[p], mask, base_log));
+            x[p].x = __int2double_rn((int)(u32)grp_decompose<st_t>(st_re[p], mask, base_log));
+            x[p].y = __int2double_rn((int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
           }
           cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw, bar_id);
           cbfft::group_sync<T>(bar_id); // last exchange of the transform fully read
@@ -217,15 +230,15 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   }
 }
 
-template <int K, int LOGN>
+template <int K, int LOGN, bool NARROW>
 __global__ void __launch_bounds__(GrpCfg<K, LOGN>::THREADS, GrpCfg<K, LOGN>::MINB)
 pbs_kernel_grp(const PbsArgs a) {
-  pbs_grp_body<K, LOGN, false>(a);
+  pbs_grp_body<K, LOGN, false, NARROW>(a);
 }
 
 // launched with cluster dimension (k+1, 1, 1): CTA rank in the cluster = polynomial index
-template <int K, int LOGN>
+template <int K, int LOGN, bool NARROW>
 __global__ void __launch_bounds__(PbsCfg<K, LOGN>::T, GrpCfg<K, LOGN>::CL_MINB)
 pbs_kernel_grp_cluster(const PbsArgs a) {
-  pbs_grp_body<K, LOGN, true>(a);
+  pbs_grp_body<K, LOGN, true, NARROW>(a);
 }

@@ -246,6 +246,7 @@ def test_pbs_large_polynomials(engine, name, n_small, bits):
     (1, 4096, 22, 1, 4.70197740328915e-38 ** 0.5),    # MESSAGE_5_CARRY_0
     (1, 8192, 15, 2, 4.70197740328915e-38 ** 0.5),    # MESSAGE_3_CARRY_3
     (4, 256, 12, 2, 2.0 ** -40), (6, 256, 10, 3, 2.0 ** -40), (3, 2048, 20, 1, 2.0 ** -60),
+    (2, 512, 17, 2, 2.0 ** -55), (1, 1024, 12, 3, 2.0 ** -55),  # base_log * level > 31: 64-bit states
 ])
 def test_pbs_reference_parameter_table(engine, k, N, b, l, sig_glwe):
     """The (k, N, base_log, level) rows of the reference's own GPU test table
