@@ -374,7 +374,7 @@ struct Variant {
   size_t grp_smem_fixed;
   bool grp_fits;
   void (*pbs_grp_cl)(const PbsArgs); // cluster variant: one CTA per polynomial
-  size_t cl_smem_fixed;
+  size_t cl_smem_fixed, cl_stash_bytes;
   bool cl_fits;
   void (*convert)(double2 *, const double2 *, size_t);
   void (*polymul)(const double *, const double *, double *, const double2 *, u32);
@@ -395,6 +395,7 @@ template <int K, int LOGN> Variant make_variant() {
   v.grp_fits = GrpCfg<K, LOGN>::FITS;
   v.pbs_grp_cl = pbs_kernel_grp_cluster<K, LOGN, true>;
   v.cl_smem_fixed = GrpCfg<K, LOGN>::CL_SMEM_FIXED;
+  v.cl_stash_bytes = GrpCfg<K, LOGN>::CL_STASH_BYTES;
   v.cl_fits = GrpCfg<K, LOGN>::CL_FITS;
   v.convert = bsk_convert_kernel<K, LOGN>;
   v.polymul = poly_mul_kernel<K, LOGN>;
@@ -486,7 +487,7 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
   }
   b->cl_cluster_cap = 0;
   if (v.cl_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
-    const size_t csmem = v.cl_smem_fixed + 4096;
+    const size_t csmem = v.cl_smem_fixed + 4096 + v.cl_stash_bytes;
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)csmem));
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl_w, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -640,7 +641,8 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(clusters * (k + 1), 1, 1);
     cfg.blockDim = dim3((u32)v.T, 1, 1);
-    cfg.dynamicSmemBytes = v.cl_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
+    cfg.dynamicSmemBytes = v.cl_stash_bytes ? v.cl_smem_fixed + 4096 + v.cl_stash_bytes
+                                            : v.cl_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     cfg.stream = stream;
     cudaLaunchAttribute attr;
     attr.id = cudaLaunchAttributeClusterDimension;

@@ -40,6 +40,11 @@ template <int K, int LOGN> struct GrpCfg {
                                       ? (int)(232448 / (CL_SMEM_FIXED + 4096))
                                       : (65536 / 128) / T;
   static constexpr int CL_MINB = CL_MINB_ < 1 ? 1 : CL_MINB_;
+  // N = 16384 (accumulator in global memory): the shared memory left next to the exchange buffer
+  // parks the real parts of the Fourier accumulators during the forward transforms of levels
+  // >= 1 (32 registers at P = 16; ptxas: 940 -> ? bytes of spills)
+  static constexpr size_t CL_STASH_OFF = CL_SMEM_FIXED + 4096;
+  static constexpr size_t CL_STASH_BYTES = C::ACC_GLOBAL ? (size_t)T * P * sizeof(double) : 0;
 };
 
 // signed digit of one level on a state of type S (iter.rs:121-133).  S = u32 is exact whenever
@@ -151,6 +156,11 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
 
 #pragma unroll 1
       for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
+        if (ACC_G && m > 0) {
+          double *stash = reinterpret_cast<double *>(smem + G::CL_STASH_OFF);
+#pragma unroll
+          for (int p = 0; p < P; ++p) stash[p * T + t] = oacc[p].x;
+        }
         {
           double2 x[P];
 #pragma unroll
@@ -162,6 +172,14 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           cbfft::group_sync<T>(bar_id); // last exchange of the transform fully read
 #pragma unroll
           for (int p = 0; p < P; ++p) fbuf[p * T + t] = x[p]; // F_{grp,m} in key order
+        }
+        if (ACC_G) { // accumulators come (back) to life only after the transform
+          const double *stash = reinterpret_cast<const double *>(smem + G::CL_STASH_OFF);
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            if (m == 0) oacc[p] = make_double2(0.0, 0.0);
+            else oacc[p].x = stash[p * T + t];
+          }
         }
         const double2 *__restrict__ g =
             a.bsk + (((size_t)i * level + m) * GS * GS + grp) * M + t;
