@@ -253,11 +253,14 @@ __device__ __forceinline__ void pack_pairs(u32 (&v)[16], const u64 (&re)[4], con
 // closest_representable + balanced digit of a one-level decomposition from the high word:
 // floor((hi + 2^(k-1)) / 2^k) taken as a signed b-bit value, except that the reference maps
 // B/2 to +B/2 (decomposer.rs:23-47, iter.rs:121-133 with state >> base_log == 0).  k = 32 - b.
-__device__ __forceinline__ int digit_l1_k(u32 hi, u32 kshift) {
-  const int sv = (int)(hi + (1u << (kshift - 1))) >> kshift;
-  const int half = 1 << (31 - kshift);
-  return (sv == -half) ? half : sv;
+// Two instructions: round-half-up of x equals minus round-half-down of -x, and an arithmetic
+// shift of (2^(k-1) - 1 - hi) is exactly that round-half-down; the result lies in [-B/2, B/2),
+// so its negation lies in (-B/2, B/2] with +B/2 at the tie, as the reference has it.  The caller
+// takes the NEGATED digit: the sign is folded into the first butterflies' FMA operands.
+__device__ __forceinline__ int neg_digit_l1_k(u32 hi, u32 kshift) {
+  return (int)(((1u << (kshift - 1)) - 1u) - hi) >> kshift;
 }
+__device__ __forceinline__ int digit_l1_k(u32 hi, u32 kshift) { return -neg_digit_l1_k(hi, kshift); }
 __device__ __forceinline__ ulonglong2 lds_u64x2(u32 addr) {
   ulonglong2 v;
   asm volatile("ld.shared.v2.u64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr));
@@ -279,8 +282,8 @@ __device__ __forceinline__ void v3_digits(double2 (&x)[32], const u32 (&v)[16], 
     const u64 rb = sw ? src.x : src.y;
     const u64 c_re = (nre ? (u64)0 - ra : ra) - own_re;
     const u64 c_im = (nim ? (u64)0 - rb : rb) - own_im;
-    x[p].x = __int2double_rn(digit_l1_k((u32)(c_re >> 32), kshift));
-    x[p].y = __int2double_rn(digit_l1_k((u32)(c_im >> 32), kshift));
+    x[p].x = -__int2double_rn(neg_digit_l1_k((u32)(c_re >> 32), kshift));
+    x[p].y = -__int2double_rn(neg_digit_l1_k((u32)(c_im >> 32), kshift));
   }
 }
 
