@@ -285,7 +285,8 @@ __device__ __forceinline__ void v3_digits(double2 (&x)[32], const u32 (&v)[16], 
     // address ^ 8 instead of selecting after a 128-bit load (4 SEL per point)
     const u32 a0 = buf_s + (sp & 0x3FF0u) + ((sp >> 11) & 8u);
     const u64 ra = lds_u64(a0), rb = lds_u64(a0 ^ 8u);
-    const bool sw = (sp & 0x4000u) != 0, nre = (sp & 0x8000u) != 0, nim = sw != nre;
+    // im is negated when bits 15 and 14 differ, i.e. when bit 15 of sp + 2^14 is set
+    const bool nre = (sp & 0x8000u) != 0, nim = ((sp + 0x4000u) & 0x8000u) != 0;
     const u64 c_re = (nre ? (u64)0 - ra : ra) - own_re;
     const u64 c_im = (nim ? (u64)0 - rb : rb) - own_im;
     x[p].x = -__int2double_rn(neg_digit_l1_k((u32)(c_re >> 32), kshift));
