@@ -267,7 +267,7 @@ void ks_imma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64
   for (u32 s0 = 0; s0 < num_samples; s0 += chunk) {
     const u32 count = std::min(chunk, num_samples - s0);
     const u32 rows = (count + imma::TM - 1) / imma::TM * imma::TM;
-    dim3 gd(std::min<u32>((n_in + 255) / 256, 8), rows);
+    dim3 gd(rows, std::min<u32>((n_in + 255) / 256, 8));
     imma::ks_digits_kernel<<<gd, 256, 0, stream>>>(D, in, in_idx, n_in, base_log, level, s0,
                                                    count, Kp);
     CB_CHECK(cudaGetLastError());

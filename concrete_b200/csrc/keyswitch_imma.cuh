@@ -48,24 +48,26 @@ __device__ __forceinline__ u64 decompose_one_level(u64 &state, u64 mask, u32 bas
   return res - (carry << base_log);
 }
 
-// D[(s - s0)][i*level + j] = j-th emitted digit of a_i (level l first), as s8.  grid (x, rows)
+// D[(s - s0)][i*level + j] = j-th emitted digit of a_i (level l first), as s8.
+// grid (rows, column blocks): the row index sits on blockIdx.x (limit 2^31 - 1), so batches of
+// more than 65 535 padded rows launch too (blockIdx.y is capped at 65 535)
 __global__ void ks_digits_kernel(signed char *__restrict__ D, const u64 *__restrict__ in,
                                  const u64 *__restrict__ in_idx, u32 n_in, u32 base_log,
                                  u32 level, u32 s0, u32 count, u32 Kp) {
-  const u32 row = blockIdx.y; // grid.y = rows padded to whole tiles
+  const u32 row = blockIdx.x; // grid.x = rows padded to whole tiles
   signed char *dst = D + (size_t)row * Kp;
   const u32 K = n_in * level;
   if (row >= count) { // padding row: zeros
-    for (u32 c = (blockIdx.x * blockDim.x + threadIdx.x) * 16; c < Kp; c += gridDim.x * blockDim.x * 16)
+    for (u32 c = (blockIdx.y * blockDim.x + threadIdx.x) * 16; c < Kp; c += gridDim.y * blockDim.x * 16)
       *reinterpret_cast<uint4 *>(dst + c) = make_uint4(0, 0, 0, 0);
     return;
   }
-  if (blockIdx.x == 0)
+  if (blockIdx.y == 0)
     for (u32 c = K + threadIdx.x; c < Kp; c += blockDim.x) dst[c] = 0; // padding columns
   const u64 *src = in + in_idx[s0 + row] * (u64)(n_in + 1);
   const u64 mask = ((u64)1 << base_log) - 1;
   const u32 state_shift = 64 - base_log * level;
-  for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n_in; i += gridDim.x * blockDim.x) {
+  for (u32 i = blockIdx.y * blockDim.x + threadIdx.x; i < n_in; i += gridDim.y * blockDim.x) {
     u64 state = closest_representable(src[i], base_log, level) >> state_shift;
     for (u32 j = 0; j < level; ++j)
       dst[i * level + j] = (signed char)(int)(u32)decompose_one_level(state, mask, base_log);

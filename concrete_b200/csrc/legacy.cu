@@ -6,6 +6,7 @@
 #include "../../include/concrete_b200.h"
 #include <map>
 #include <mutex>
+#include <vector>
 
 void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
                          const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
@@ -25,26 +26,27 @@ __global__ void k_iota(u64 *p, u32 n) {
   for (u32 i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = i;
 }
 
-// Per-device identity index array 0..cap-1, grown on demand.  The legacy ABI has no index
-// arguments; the current kernels take them.  Growth synchronises the device once (rare).
+// Per-device identity index array 0..cap-1.  The legacy ABI has no index arguments; the current
+// kernels take them.  Arrays are filled on a private non-blocking stream that only the calling
+// host thread waits for (no device-wide synchronisation, nothing on the NULL stream), and an
+// array that has been handed out is never freed: growth allocates a larger one and keeps the old
+// pointers valid for callers that fetched them concurrently (bounded: capacities double).
 std::mutex g_iota_mutex;
-struct Iota { u64 *ptr = nullptr; u32 cap = 0; };
+struct Iota { u64 *ptr = nullptr; u32 cap = 0; cudaStream_t fill = nullptr; std::vector<u64 *> old; };
 std::map<int, Iota> g_iota;
 
 const u64 *identity_indexes(int gpu, u32 n) {
   std::lock_guard<std::mutex> g(g_iota_mutex);
   Iota &it = g_iota[gpu];
   if (it.cap >= n) return it.ptr;
-  u32 cap = 1024;
+  u32 cap = 1u << 20; // 8 MB: covers every batch the runtime sends without ever growing
   while (cap < n) cap <<= 1;
-  if (it.ptr) {
-    CB_CHECK(cudaDeviceSynchronize());
-    CB_CHECK(cudaFree(it.ptr));
-  }
+  if (!it.fill) CB_CHECK(cudaStreamCreateWithFlags(&it.fill, cudaStreamNonBlocking));
+  if (it.ptr) it.old.push_back(it.ptr);
   CB_CHECK(cudaMalloc((void **)&it.ptr, (size_t)cap * sizeof(u64)));
-  k_iota<<<(cap + 255) / 256, 256>>>(it.ptr, cap);
+  k_iota<<<(cap + 255) / 256, 256, 0, it.fill>>>(it.ptr, cap);
   CB_CHECK(cudaGetLastError());
-  CB_CHECK(cudaDeviceSynchronize());
+  CB_CHECK(cudaStreamSynchronize(it.fill));
   CB_LAUNCHED();
   it.cap = cap;
   return it.ptr;

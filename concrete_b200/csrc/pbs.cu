@@ -133,13 +133,11 @@ struct PbsArgs {
   const double2 *tw;
   ulonglong2 *global_acc; // [gridDim.x][(K+1)*M] pairs, only when ACC_GLOBAL
   u32 n, base_log, level, num_samples, lut_count, lut_stride;
-  u32 cpb_active; // w32 v2 experiment: ciphertexts per CTA actually used (1..4)
-  u32 skew_ns; // w32 v2: start-up phase offset between the ciphertexts of a CTA
 };
 
 } // namespace
+#include "sm100_prims.cuh"
 #include "pbs_w32.cuh"
-#include "pbs_w32_v2.cuh"
 #include "pbs_w32_v3.cuh"
 namespace {
 
@@ -560,35 +558,13 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
     a.num_samples = num_samples;
     a.lut_count = lut_count;
     a.lut_stride = lut_stride;
-    static const char *skew_env = std::getenv("CONCRETE_B200_SKEW_NS");
-    a.skew_ns = skew_env ? (u32)std::atoi(skew_env) : 0;
-    static const char *cpb_env = std::getenv("CONCRETE_B200_CPB");
-    a.cpb_active = cpb_env ? (u32)std::atoi(cpb_env) : 4;
     int sms = 0;
     CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
-    static const char *ver_env = std::getenv("CONCRETE_B200_W32");
-    static const int ver = ver_env ? std::atoi(ver_env) : 3;
-    if (ver == 1) {
-      CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)w32::SMEM_BYTES));
-      const u32 ctas = (num_samples + w32::CPB - 1) / w32::CPB;
-      const u32 grid = std::min<u32>((u32)sms, ctas);
-      w32::pbs_kernel_w32<<<grid, w32::NTHREADS, w32::SMEM_BYTES, stream>>>(a);
-    } else if (ver == 2) {
-      CB_CHECK(cudaFuncSetAttribute(w32::pbs_kernel_w32v2,
-                                    cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)w32::SMEM_BYTES2));
-      const u32 ctas = (num_samples + a.cpb_active - 1) / a.cpb_active;
-      const u32 grid = std::min<u32>((u32)sms, ctas);
-      w32::pbs_kernel_w32v2<<<grid, w32::NTHREADS2, w32::SMEM_BYTES2, stream>>>(a);
-    } else {
-      auto kern = w32::pbs_kernel_w32v3;
-      CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)w32::SMEM_BYTES3));
-      const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
-      kern<<<grid, w32::NTHREADS3, w32::SMEM_BYTES3, stream>>>(a);
-    }
+    auto kern = w32::pbs_kernel_w32v3;
+    CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)w32::SMEM_BYTES3));
+    const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
+    kern<<<grid, w32::NTHREADS3, w32::SMEM_BYTES3, stream>>>(a);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
     return;
@@ -616,7 +592,6 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   a.num_samples = num_samples;
   a.lut_count = lut_count;
   a.lut_stride = lut_stride;
-  a.skew_ns = 0;
   // The cluster variant (one CTA per polynomial, F through DSMEM) is bit-compatible and fits
   // N = 8192, but measured slower than the first kernel there (P7: 671 vs 633 ms: two cluster
   // barriers per CMUX with one CTA per SM); it stays selectable for experiments and tests.

@@ -16,6 +16,8 @@
 #pragma once
 
 namespace w32 {
+using namespace sm100;
+using namespace sm100;
 
 constexpr int CPB2 = 4;
 constexpr int NTHREADS2 = 64 * CPB2;

@@ -114,6 +114,21 @@ def test_keyswitch_decomposition_shapes(engine, n_in, n_out, b_ks, l_ks, num):
     assert np.array_equal(got, ref)
 
 
+def test_keyswitch_more_than_65535_rows(engine):
+    """Small K (n_in * l_ks < 4096) and a batch above the 65 535 grid.y limit in ONE chunk of the
+    INT8 tensor-core path: the digit kernel's row index must not sit on blockIdx.y."""
+    from concrete_b200 import as_u64
+
+    n_in, n_out, b_ks, l_ks, num = 96, 17, 4, 3, 70001
+    rng = np.random.default_rng(99)
+    ksk = rng.integers(0, 2 ** 64, size=n_in * l_ks * (n_out + 1), dtype=np.uint64)
+    cts = rng.integers(0, 2 ** 64, size=(num, n_in + 1), dtype=np.uint64)
+    ref = orc.keyswitch(cts, ksk, n_in, n_out, b_ks, l_ks)
+    got = as_u64(engine.keyswitch(engine.to_device(cts), engine.upload_ksk(ksk), n_in, n_out,
+                                  b_ks, l_ks))
+    assert np.array_equal(got, ref)
+
+
 def test_keyswitch_empty_batch(engine):
     import torch
 
