@@ -45,6 +45,8 @@ def parse_args():
     ap.add_argument("--workload", default="P2048")
     ap.add_argument("--samples", type=int, default=16384, help="ciphertexts per GPU per step")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
+    ap.add_argument("--pbs-plan", type=int, default=0,
+                    help="test hook: pin the PBS kernel family (see include/concrete_b200.h)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true",
@@ -208,6 +210,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     eng = Engine(local)
     lib = eng.lib
+    if args.pbs_plan:
+        lib.concrete_b200_set_pbs_plan(args.pbs_plan)
     p = PARAMS[args.workload]
     S = args.samples
 

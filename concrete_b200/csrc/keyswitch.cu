@@ -202,10 +202,13 @@ namespace {
 // Tensor-core path (keyswitch_imma.cuh).  Chosen when the batch fills the GEMM tiles and the
 // exactness conditions hold: digits fit s8 (|d| <= B/2 <= 64) and the s32 accumulators cannot
 // wrap (B/2 * 255 * K < 2^31).  Otherwise the IMAD kernel below runs; both are bit-exact.
+// concrete_b200_set_ks_plan(): TEST hook.  0 = automatic, 1 = integer-pipe kernel, 2 = INT8
+// tensor-core kernel whenever it is exact (also for batches below 512).
+std::atomic<int> g_ks_plan{0};
 bool ks_imma_eligible(u32 n_in, u32 base_log, u32 level, u32 num_samples) {
-  static const char *env = std::getenv("CONCRETE_B200_KS");
-  if (env && std::string(env) == "imad") return false;
-  const bool forced = env && std::string(env) == "imma";
+  const int plan = g_ks_plan.load(std::memory_order_relaxed);
+  if (plan == 1) return false;
+  const bool forced = plan == 2;
   if (base_log > 7) return false;
   const u64 K = (u64)n_in * level;
   if ((K << (base_log - 1)) * 255 >= ((u64)1 << 31)) return false;
@@ -331,6 +334,10 @@ void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, cons
                                         level, num_samples, KI, tiles_per_split, use_atomics);
   CB_CHECK(cudaGetLastError());
   CB_LAUNCHED();
+}
+
+extern "C" void concrete_b200_set_ks_plan(int plan) {
+  g_ks_plan.store(plan, std::memory_order_relaxed);
 }
 
 extern "C" void cuda_keyswitch_lwe_ciphertext_vector_64(

@@ -16,87 +16,19 @@
 // read straight from L2 with 16-byte coalesced loads in the very order the registers need it,
 // and mod-switch / rotation / gadget decomposition / FFT / product / inverse FFT / torus rounding
 // / sample extraction never leave the SM.
-#include "common.cuh"
-#include "fft.cuh"
-#include "../../include/concrete_b200.h"
-#include <cmath>
-#include <type_traits>
+#include "pbs_common.cuh"
+#include <atomic>
 #include <cooperative_groups.h>
-#include <map>
-#include <mutex>
-#include <vector>
+
+// pbs_v4.cu
+bool cb_pbs_v4_shape(u32 k, u32 N);
+void cb_pbs_v4_convert(cudaStream_t stream, int gpu, void *dest, size_t polys, u32 k, u32 N);
+void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_idx,
+                      const u64 *lut_vector, const u64 *lut_idx, const u64 *lwe_in,
+                      const u64 *in_idx, const double2 *bsk, u32 n, u32 k, u32 N, u32 base_log,
+                      u32 level, u32 num_samples, u32 lut_count, u32 lut_stride);
 
 namespace {
-
-// ------------------------------------------------------------------------------------------
-// Twiddle tables: tw[2^s + b] = exp(i*pi*(1 + 4*bitrev_s(b)) / 2^(s+2)), one per (device, LOGM)
-// ------------------------------------------------------------------------------------------
-void cb_w32_set_const_twiddles(const double2 *host_tw); // defined after pbs_w32.cuh
-std::mutex g_tw_mutex;
-std::map<std::pair<int, int>, double2 *> g_tw_cache;
-
-u32 bitrev(u32 x, int bits) {
-  u32 r = 0;
-  for (int i = 0; i < bits; ++i) r = (r << 1) | ((x >> i) & 1);
-  return r;
-}
-
-const double2 *get_twiddles(int gpu, int logm) {
-  std::lock_guard<std::mutex> g(g_tw_mutex);
-  auto key = std::make_pair(gpu, logm);
-  auto it = g_tw_cache.find(key);
-  if (it != g_tw_cache.end()) return it->second;
-  const size_t M = (size_t)1 << logm;
-  std::vector<double2> h(M);
-  h[0] = make_double2(1.0, 0.0);
-  const long double pi = 3.14159265358979323846264338327950288L;
-  for (int s = 0; s < logm; ++s)
-    for (u32 b = 0; b < (1u << s); ++b) {
-      long double ang = pi * (long double)(1 + 4 * (uint64_t)bitrev(b, s)) /
-                        (long double)((uint64_t)1 << (s + 2));
-      h[((size_t)1 << s) + b] = make_double2((double)cosl(ang), (double)sinl(ang));
-    }
-  double2 *d = nullptr;
-  CB_CHECK(cudaMalloc(&d, M * sizeof(double2)));
-  CB_CHECK(cudaMemcpy(d, h.data(), M * sizeof(double2), cudaMemcpyHostToDevice));
-  if (logm == 10) cb_w32_set_const_twiddles(h.data()); // current device == gpu
-  { // generic constant table: entries [0, min(M, 256)) are the same for every size
-    static std::map<int, size_t> filled; // per device: how many entries are valid
-    const size_t want = std::min<size_t>(M, (size_t)cbfft::CONST_TW);
-    if (filled[gpu] < want) {
-      CB_CHECK(cudaMemcpyToSymbol(cbfft::c_twg, h.data(), want * sizeof(double2)));
-      filled[gpu] = want;
-    }
-  }
-  g_tw_cache[key] = d;
-  return d;
-}
-
-// ------------------------------------------------------------------------------------------
-// Integer helpers (restate decomposer.rs:23-47, iter.rs:121-133, fft_impl/common.rs:17-25,
-// commons/math/torus/mod.rs:72-78)
-// ------------------------------------------------------------------------------------------
-__device__ __forceinline__ u64 closest_representable(u64 x, u32 shift_m1) {
-  u64 r = x >> shift_m1;
-  r += 1;
-  r &= ~(u64)1;
-  return r << shift_m1;
-}
-__device__ __forceinline__ u64 decompose_one_level(u64 &state, u64 mask, u32 base_log) {
-  u64 res = state & mask;
-  state >>= base_log;
-  u64 carry = ((res - 1) | state) & res;
-  carry >>= (base_log - 1);
-  state += carry;
-  return res - (carry << base_log);
-}
-__device__ __forceinline__ u32 modulus_switch(u64 x, u32 log_modulus) {
-  return (u32)((x + ((u64)1 << (63 - log_modulus))) >> (64 - log_modulus));
-}
-__device__ __forceinline__ u64 from_torus(double x) {
-  double fr = x - rint(x);
-  return (u64)__double2ll_rn(fr * 18446744073709551616.0);
-}
 
 // ------------------------------------------------------------------------------------------
 // Kernel configuration per (K, LOGN)
@@ -122,18 +54,6 @@ template <int K, int LOGN> struct PbsCfg {
   static constexpr bool ACC_GLOBAL = (FBUF_BYTES + ACC_BYTES + 4096) > 232448;
 };
 
-struct PbsArgs {
-  u64 *lwe_out;
-  const u64 *out_idx;
-  const u64 *lut_vector;
-  const u64 *lut_idx;
-  const u64 *lwe_in;
-  const u64 *in_idx;
-  const double2 *bsk;
-  const double2 *tw;
-  ulonglong2 *global_acc; // [gridDim.x][(K+1)*M] pairs, only when ACC_GLOBAL
-  u32 n, base_log, level, num_samples, lut_count, lut_stride;
-};
 
 } // namespace
 #include "sm100_prims.cuh"
@@ -144,7 +64,23 @@ namespace {
 void cb_w32_set_const_twiddles(const double2 *host_tw) {
   CB_CHECK(cudaMemcpyToSymbol(w32::c_tw, host_tw, 32 * sizeof(double2)));
 }
-// the warp-per-polynomial kernels cover exactly this shape (BASELINE.json configs[1])
+const bool g_tw_hook_installed = (g_tw_hook_logm10 = cb_w32_set_const_twiddles, true);
+
+// ------------------------------------------------------------------------------------------
+// Kernel plan.  Which fused kernel serves a shape is a pure function of (k, N, level) — it has to
+// be: the Fourier key layout is private to the kernel family and is chosen when the key is
+// converted, long before the first PBS call.  Families:
+//   W32      pbs_w32_v3.cuh   k = 1, N = 2048, l = 1 (BASELINE.json configs[1])
+//   V4       pbs_v4.cuh       k = 1, N = 1024..8192 and k = 2, N = 1024, any l
+//   GENERIC  pbs_grp.cuh / pbs_kernel: every other (k, N) of the reference, and N = 16384
+// concrete_b200_set_pbs_plan() is a TEST hook (tests keep the older kernels covered): it must be
+// called before the key is converted.  0 = automatic.
+// ------------------------------------------------------------------------------------------
+enum { PLAN_AUTO = 0, PLAN_GENERIC = 1, PLAN_GRP = 2, PLAN_CLUSTER = 3, PLAN_V4 = 4 };
+std::atomic<int> g_pbs_plan{PLAN_AUTO};
+enum Family { FAM_W32, FAM_V4, FAM_GENERIC };
+
+// the warp-per-polynomial kernel covers exactly this shape
 inline bool use_w32(u32 k, u32 N, u32 level) { return k == 1 && N == 2048 && level == 1; }
 
 template <int K, int LOGN>
@@ -424,6 +360,15 @@ bool get_variant(u32 k, u32 N, Variant &v) {
   return false;
 }
 
+Family key_family(u32 k, u32 N, u32 level) {
+  const int plan = g_pbs_plan.load(std::memory_order_relaxed);
+  if (plan == PLAN_GENERIC || plan == PLAN_GRP || plan == PLAN_CLUSTER) return FAM_GENERIC;
+  if (plan == PLAN_V4 && cb_pbs_v4_shape(k, N)) return FAM_V4;
+  if (use_w32(k, N, level)) return FAM_W32;
+  if (cb_pbs_v4_shape(k, N)) return FAM_V4;
+  return FAM_GENERIC;
+}
+
 constexpr u32 PBS_MAGIC = 0xB200CB01u;
 
 struct PbsBuffer {
@@ -473,7 +418,7 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
     CB_PANIC("Cuda error (classical PBS): kernel does not fit on an SM (smem %zu B)", smem);
   b->grid_cap = per_sm * sms;
   b->grp_grid_cap = 0;
-  if (v.grp_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
+  if (v.grp_fits) {
     const size_t gsmem = v.grp_smem_fixed + 4096;
     int occ = 0;
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -484,7 +429,7 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
     b->grp_grid_cap = occ * sms;
   }
   b->cl_cluster_cap = 0;
-  if (v.cl_fits && !std::getenv("CONCRETE_B200_NO_GRP")) {
+  if (v.cl_fits) {
     const size_t csmem = v.cl_smem_fixed + 4096 + v.cl_stash_bytes;
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_cl, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)csmem));
@@ -541,7 +486,13 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   if (lut_count == 0) lut_count = 1;
   if ((u64)(lut_count - 1) * lut_stride >= N)
     CB_PANIC("Cuda error (classical PBS): lut_count*lut_stride exceeds polynomial size");
-  if (use_w32(k, N, level)) {
+  const Family fam = key_family(k, N, level);
+  if (fam == FAM_V4) {
+    cb_pbs_v4_launch(stream, gpu, lwe_out, out_idx, lut_vector, lut_idx, lwe_in, in_idx, bsk, n, k,
+                     N, base_log, level, num_samples, lut_count, lut_stride);
+    return;
+  }
+  if (fam == FAM_W32) {
     PbsArgs a;
     a.lwe_out = lwe_out;
     a.out_idx = out_idx;
@@ -598,10 +549,11 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   // Exception: when the accumulator lives in global memory anyway (N = 16384) the cluster
   // variant is the default: one polynomial per CTA keeps 16 points per thread in 128 registers
   // where the first kernel is capped at 64 registers with 2 KB of spills per thread.
+  const int plan = g_pbs_plan.load(std::memory_order_relaxed);
   const bool force_cluster =
-      std::getenv("CONCRETE_B200_FORCE_CLUSTER") != nullptr ||
-      (v.acc_global && b->global_acc && !std::getenv("CONCRETE_B200_NO_CLUSTER"));
-  if (b->grp_grid_cap > 0 && n <= 2048 && !(force_cluster && b->cl_cluster_cap > 0)) {
+      plan == PLAN_CLUSTER || (plan != PLAN_GENERIC && v.acc_global && b->global_acc);
+  if (plan != PLAN_GENERIC && b->grp_grid_cap > 0 && n <= 2048 &&
+      !(force_cluster && b->cl_cluster_cap > 0)) {
     const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
     (base_log * level <= 31 ? v.pbs_grp : v.pbs_grp_w)<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
@@ -652,7 +604,12 @@ void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_ho
   const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
   int sms = 0;
   CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
-  if (use_w32(k, N, level)) {
+  const Family fam = key_family(k, N, level);
+  if (fam == FAM_V4) {
+    cb_pbs_v4_convert(stream, gpu, dest, polys, k, N);
+    return;
+  }
+  if (fam == FAM_W32) {
     const size_t smem = w32::SMEM_TW + 4 * (size_t)w32::M * sizeof(double2);
     CB_CHECK(cudaFuncSetAttribute(w32::bsk_convert_kernel_w32,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -672,6 +629,9 @@ void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_ho
 }
 
 extern "C" {
+
+// test hook, see "Kernel plan" above
+void concrete_b200_set_pbs_plan(int plan) { g_pbs_plan.store(plan, std::memory_order_relaxed); }
 
 void cuda_convert_lwe_programmable_bootstrap_key_64(void *stream, uint32_t gpu_index, void *dest,
                                                     void *src, uint32_t input_lwe_dim,
@@ -762,7 +722,7 @@ void cuda_fourier_polynomial_mul(void *stream, uint32_t gpu_index, void *input1,
     CB_PANIC("Cuda error (fourier mul): unsupported polynomial size %u", polynomial_size);
   const double2 *tw =
       get_twiddles(gpu_index, (int)std::lround(std::log2((double)polynomial_size)) - 1);
-  if (polynomial_size == 2048 && !std::getenv("CONCRETE_B200_GENERIC_FFT")) {
+  if (polynomial_size == 2048) {
     const size_t smem = w32::SMEM_TW + 4 * (size_t)w32::M * sizeof(double2);
     CB_CHECK(cudaFuncSetAttribute(w32::poly_mul_kernel_w32,
                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

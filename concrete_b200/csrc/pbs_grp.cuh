@@ -47,18 +47,6 @@ template <int K, int LOGN> struct GrpCfg {
   static constexpr size_t CL_STASH_BYTES = C::ACC_GLOBAL ? (size_t)T * P * sizeof(double) : 0;
 };
 
-// signed digit of one level on a state of type S (iter.rs:121-133).  S = u32 is exact whenever
-// base_log * level <= 31 (the state has base_log * level bits) and halves the registers the
-// decomposition states hold across the transforms of a multi-level CMUX.
-template <class S> __device__ __forceinline__ S grp_decompose(S &state, S mask, u32 base_log) {
-  S res = state & mask;
-  state >>= base_log;
-  S carry = ((res - 1) | state) & res;
-  carry >>= (base_log - 1);
-  state += carry;
-  return res - (carry << base_log);
-}
-
 template <int K, int LOGN, bool CLUSTER, bool NARROW>
 __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   using st_t = typename std::conditional<NARROW, u32, u64>::type;

@@ -1,0 +1,107 @@
+// pbs_v4.cu — host side of the v4 fused PBS kernels (pbs_v4.cuh): which (k, N) shapes they cover,
+// the BSK -> Fourier conversion into their key layout, and the launch.  Own translation unit so
+// that the fifteen kernel instantiations compile in parallel with pbs.cu.
+#include "pbs_common.cuh"
+#include "sm100_prims.cuh"
+#include "pbs_v4.cuh"
+
+namespace {
+
+struct V4Variant {
+  void (*one_level)(const PbsArgs);    // l = 1
+  void (*multi_narrow)(const PbsArgs); // l >= 2, base_log * l <= 31 (32-bit decomposition states)
+  void (*multi_wide)(const PbsArgs);   // l >= 2, base_log * l  > 31
+  void (*convert)(double2 *, const double2 *, size_t);
+  int threads, T, cpb, logm;
+  size_t smem, smem_stash, convert_smem;
+};
+
+template <int K, int LOGN, int CPB> V4Variant make_v4() {
+  using C1 = v4::Cfg<K, LOGN, 4, CPB, false>;
+  using CL = v4::Cfg<K, LOGN, 4, CPB, true>;
+  V4Variant v;
+  v.one_level = v4::pbs_kernel_v4<C1, true, 1>;
+  v.multi_narrow = v4::pbs_kernel_v4<CL, true, 0>;
+  v.multi_wide = v4::pbs_kernel_v4<CL, false, 0>;
+  v.convert = v4::bsk_convert_kernel_v4<C1>;
+  v.threads = C1::THREADS;
+  v.T = C1::T;
+  v.cpb = CPB;
+  v.logm = C1::LOGM;
+  v.smem = C1::SMEM;
+  v.smem_stash = CL::SMEM;
+  v.convert_smem = C1::BUF_BYTES;
+  return v;
+}
+
+// shapes: every k = 1 polynomial size of the BASELINE configs from 1024 up to 8192, and P4's
+// (k = 2, N = 1024).  N = 16384 needs the two polynomials of a ciphertext on two SMs (256 KiB of
+// accumulator): see pbs_v4 cluster notes in DESIGN.md.
+bool v4_variant(u32 k, u32 N, V4Variant &v) {
+  if (k == 1 && N == 1024) { v = make_v4<1, 10, 8>(); return true; }
+  if (k == 1 && N == 2048) { v = make_v4<1, 11, 4>(); return true; }
+  if (k == 1 && N == 4096) { v = make_v4<1, 12, 2>(); return true; }
+  if (k == 1 && N == 8192) { v = make_v4<1, 13, 1>(); return true; }
+  if (k == 2 && N == 1024) { v = make_v4<2, 10, 5>(); return true; }
+  return false;
+}
+
+} // namespace
+
+bool cb_pbs_v4_shape(u32 k, u32 N) {
+  return (k == 1 && (N == 1024 || N == 2048 || N == 4096 || N == 8192)) || (k == 2 && N == 1024);
+}
+
+int cb_pbs_v4_cpb(u32 k, u32 N) {
+  V4Variant v;
+  return v4_variant(k, N, v) ? v.cpb : 0;
+}
+
+// the standard-domain key is already in `dest` (device); transform every polynomial in place
+void cb_pbs_v4_convert(cudaStream_t stream, int gpu, void *dest, size_t polys, u32 k, u32 N) {
+  V4Variant v;
+  if (!v4_variant(k, N, v)) CB_PANIC("Cuda error (convert BSK, v4): unsupported shape");
+  const double2 *tw = get_twiddles(gpu, v.logm);
+  int sms = 0;
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  CB_CHECK(cudaFuncSetAttribute(v.convert, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.convert_smem));
+  const u32 grid = (u32)std::min<size_t>(polys, (size_t)sms * 8);
+  v.convert<<<grid, v.T, v.convert_smem, stream>>>(reinterpret_cast<double2 *>(dest), tw, polys);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_idx,
+                      const u64 *lut_vector, const u64 *lut_idx, const u64 *lwe_in,
+                      const u64 *in_idx, const double2 *bsk, u32 n, u32 k, u32 N, u32 base_log,
+                      u32 level, u32 num_samples, u32 lut_count, u32 lut_stride) {
+  V4Variant v;
+  if (!v4_variant(k, N, v)) CB_PANIC("Cuda error (classical PBS, v4): unsupported shape");
+  PbsArgs a;
+  a.lwe_out = lwe_out;
+  a.out_idx = out_idx;
+  a.lut_vector = lut_vector;
+  a.lut_idx = lut_idx;
+  a.lwe_in = lwe_in;
+  a.in_idx = in_idx;
+  a.bsk = bsk;
+  a.tw = get_twiddles(gpu, v.logm);
+  a.global_acc = nullptr;
+  a.n = n;
+  a.base_log = base_log;
+  a.level = level;
+  a.num_samples = num_samples;
+  a.lut_count = lut_count;
+  a.lut_stride = lut_stride;
+  void (*kern)(const PbsArgs) =
+      level == 1 ? v.one_level : (base_log * level <= 31 ? v.multi_narrow : v.multi_wide);
+  const size_t smem = level == 1 ? v.smem : v.smem_stash;
+  CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int sms = 0;
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
+  kern<<<grid, v.threads, smem, stream>>>(a);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}

@@ -1,0 +1,597 @@
+// pbs_v4.cuh — fused PBS for every (k, N, l) with N >= 1024: the v3 data flow (pbs_w32_v3.cuh)
+// generalised.  Included by pbs.cu inside its anonymous namespace.
+//
+// What ncu said about the kernels this replaces (profiles/r2_base_{P4,P6,P7,P8}_*.txt): all four
+// are latency-bound (no eligible warp 60-80 % of the cycles) — Fourier-key LDGs straight from
+// L2/HBM in the product (long scoreboard), one CTA of 16 warps per SM because accumulator +
+// exchange buffers fill the shared memory, spills at N >= 8192 and, at N = 16384, the accumulator
+// in global memory.  Here:
+//   * a GROUP of T = M/P threads owns one GLWE polynomial of one ciphertext, P = 16 Fourier points
+//     per thread (3 register passes for M = 2048..8192 instead of 4 with P = 8);
+//   * the polynomial's shared-memory buffer (M x 16 B) is the accumulator's home between CMUXes
+//     (rotated gather of ACC*X^a), THEN the exchange buffer of the transforms, THEN the parking
+//     place of the forward transform for the partner groups: half the shared memory of the
+//     group kernel, so CPB ciphertexts fit where one did;
+//   * the thread's own accumulator pairs live in TENSOR MEMORY (tcgen05.ld/st 32x32b), which is
+//     what makes that aliasing possible; for l >= 2 the Fourier accumulators are parked there too
+//     during the next level's forward transform (no spills, no global-memory accumulator);
+//   * the Fourier GGSW streams through a 4-slot shared-memory ring by bulk TMA copies
+//     (cp.async.bulk + mbarrier complete_tx), one fill = row p (of P) of the (k+1)^2 polynomials
+//     of one level, shared by every ciphertext of the CTA; slot and parity of a fill are
+//     compile-time constants (P fills per level = a whole even number of ring revolutions);
+//   * exchanges are XOR-swizzled (conflict-free for every pass pattern), the key and the parked
+//     transform are stored [p][t] (conflict-free LDS.128).
+// Arithmetic: identical to pbs_kernel / pbs_kernel_grp (same rounding, same transforms, same
+// key scaling); restates bootstrap.rs:250-368, ggsw.rs:481-602, glwe_sample_extraction.rs:90-165.
+#pragma once
+
+namespace v4 {
+using namespace sm100;
+
+template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_> struct Cfg {
+  static constexpr int K = K_, LOGN = LOGN_, LOGM = LOGN_ - 1, M = 1 << LOGM, N = 2 * M;
+  static constexpr int LOGP = LOGP_, P = 1 << LOGP_, T = M / P;
+  static constexpr int GS = K_ + 1, CPB = CPB_, GROUPS = CPB_ * GS, THREADS = GROUPS * T;
+  static constexpr int NWARPS = THREADS / 32;
+  static constexpr bool STASH = STASH_; // l >= 2: Fourier accumulators parked in TMEM
+  static constexpr u32 BUF_BYTES = (u32)M * 16;
+  static constexpr u32 ROW_BYTES = (u32)T * 16;               // row p of one key polynomial
+  static constexpr u32 FILL_BYTES = (u32)GS * GS * ROW_BYTES; // row p of one GGSW level
+  static constexpr int SLOTS = 4;
+  static constexpr u32 OFF_RING = (u32)GROUPS * BUF_BYTES;
+  static constexpr u32 OFF_CTRL = OFF_RING + SLOTS * FILL_BYTES;
+  static constexpr size_t SMEM = (size_t)OFF_CTRL + 128;
+  static constexpr u32 TM_OWN = 4 * P;                           // columns of a thread's own pairs
+  static constexpr u32 TM_PER_WARP = TM_OWN * (STASH_ ? 2 : 1);
+  static constexpr int NPASS = (LOGM + LOGP - 1) / LOGP;
+  static_assert(T >= 32 && T % 32 == 0, "a group is a whole number of warps");
+  static_assert(THREADS <= 1024 && THREADS % 32 == 0, "CTA size");
+  static_assert(((NWARPS + 3) / 4) * TM_PER_WARP <= 512, "TMEM columns");
+  static_assert((P / SLOTS) % 2 == 0, "static mbarrier parity needs an even number of revolutions");
+  static_assert(SMEM <= 232448, "shared memory");
+  static_assert(T == 32 || CPB_ + GROUPS <= 15, "named barriers");
+};
+
+struct Ctrl {
+  unsigned long long full_bar[4];
+  unsigned int done_cnt[4];
+  unsigned int tmem_base;
+  unsigned int n, level, base_log, total_fills;
+  const double2 *bsk, *tw;
+};
+
+// Fresh, opaque read of the thread index: every phase of the CMUX re-derives its few address
+// bases from it instead of keeping them (or, worse, every swizzled address of every exchange)
+// live across the transforms — at 128 registers with 64 of them holding Fourier points there is
+// no room for hoisted loop invariants (same device as pbs_w32_v3.cuh's V3Phase).
+__device__ __forceinline__ int opaque_tid() {
+  u32 tid;
+  asm volatile("mov.u32 %0, %%tid.x;" : "=r"(tid));
+  return (int)tid;
+}
+// twiddle load that stays where it is written (no hoisting above the previous stage)
+__device__ __forceinline__ double2 ldg_tw(const double2 *p) {
+  double2 w;
+  asm volatile("ld.global.nc.v2.f64 {%0, %1}, [%2];" : "=d"(w.x), "=d"(w.y) : "l"(p));
+  return w;
+}
+
+template <class C> __device__ __forceinline__ void grp_bar(int grp) {
+  if constexpr (C::T == 32) {
+    __syncwarp();
+  } else {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + C::CPB + grp), "n"(C::T) : "memory");
+  }
+}
+template <class C> __device__ __forceinline__ void ct_bar(int ct) {
+  asm volatile("bar.sync %0, %1;" ::"r"(1 + ct), "n"(C::GS * C::T) : "memory");
+}
+
+// ---- transforms: the passes of fft.cuh with an XOR-swizzled exchange ---------------------------
+template <class C> __device__ __forceinline__ int swz(int idx) {
+  return idx ^ ((idx >> C::LOGP) & 7);
+}
+template <class C> __device__ __forceinline__ constexpr int pass_lo(int pass) {
+  return (pass == C::NPASS - 1) ? 0 : (C::LOGM - C::LOGP * (pass + 1));
+}
+
+// stages [s_begin, s_end) on in-thread data (fft.cuh fwd_stages / inv_stages with pinned loads)
+template <class C>
+__device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, int s_begin,
+                                           int s_end, const double2 *__restrict__ tw) {
+  constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
+#pragma unroll
+  for (int s = s_begin; s < s_end; ++s) {
+    const int beta = LOGM - 1 - s, rho = beta - lo;
+#pragma unroll
+    for (int r = 0; r < P; ++r) {
+      if (r & (1 << rho)) continue;
+      if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
+      const int idx = cbfft::elem_index<LOGP>(t, r, lo);
+      const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
+      const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
+      const double2 w = first_pass ? cbfft::c_twg[(1 << s) + b] : ldg_tw(&tw[(1 << s) + b]);
+      cbfft::bfly_ct(x[r], x[r | (1 << rho)], w);
+      if (rho + 1 < LOGP) {
+        const int r2 = r | (1 << (rho + 1));
+        cbfft::bfly_ct(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
+      }
+    }
+  }
+}
+template <class C>
+__device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, int s_hi, int s_lo,
+                                           const double2 *__restrict__ tw) {
+  constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
+#pragma unroll
+  for (int s = s_hi - 1; s >= s_lo; --s) {
+    const int beta = LOGM - 1 - s, rho = beta - lo;
+#pragma unroll
+    for (int r = 0; r < P; ++r) {
+      if (r & (1 << rho)) continue;
+      if (rho + 1 < LOGP && (r & (1 << (rho + 1)))) continue;
+      const int idx = cbfft::elem_index<LOGP>(t, r, lo);
+      const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
+      const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
+      const double2 w = first_pass ? cbfft::c_twg[(1 << s) + b] : ldg_tw(&tw[(1 << s) + b]);
+      cbfft::bfly_gs(x[r], x[r | (1 << rho)], w);
+      if (rho + 1 < LOGP) {
+        const int r2 = r | (1 << (rho + 1));
+        cbfft::bfly_gs(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
+      }
+    }
+  }
+}
+
+// In: x[r] = z_{t + r*T}.  Out: x[r] = F_{q = t*P + r}.  Every exchange is barrier / write /
+// barrier / read, so the buffer may have other readers right up to the call.
+template <class C>
+__device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__restrict__ tw) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+#pragma unroll
+  for (int pass = 0; pass < C::NPASS; ++pass) {
+    const int tid = opaque_tid(), t = tid % C::T, grp = tid / C::T;
+    double2 *buf = reinterpret_cast<double2 *>(smem + (size_t)grp * C::BUF_BYTES);
+    const int lo = pass_lo<C>(pass);
+    const int s0 = pass * C::LOGP;
+    const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
+    fwd_stages<C>(x, t, lo, s0, s1, tw);
+    if (pass + 1 < C::NPASS) {
+      const int lo2 = pass_lo<C>(pass + 1);
+      grp_bar<C>(grp);
+#pragma unroll
+      for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
+      grp_bar<C>(grp);
+#pragma unroll
+      for (int r = 0; r < C::P; ++r) x[r] = buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo2))];
+    }
+  }
+}
+
+// In: x[r] = F_{t*P + r}.  Out: x[r] = M * z_{t + r*T} (unnormalised).
+template <class C>
+__device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__restrict__ tw) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+#pragma unroll
+  for (int pass = C::NPASS - 1; pass >= 0; --pass) {
+    const int tid = opaque_tid(), t = tid % C::T, grp = tid / C::T;
+    double2 *buf = reinterpret_cast<double2 *>(smem + (size_t)grp * C::BUF_BYTES);
+    const int lo = pass_lo<C>(pass);
+    const int s0 = pass * C::LOGP;
+    const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
+    inv_stages<C>(x, t, lo, s1, s0, tw);
+    if (pass > 0) {
+      const int lo2 = pass_lo<C>(pass - 1);
+      grp_bar<C>(grp);
+#pragma unroll
+      for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
+      grp_bar<C>(grp);
+#pragma unroll
+      for (int r = 0; r < C::P; ++r) x[r] = buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo2))];
+    }
+  }
+}
+
+// ---- key ring -----------------------------------------------------------------------------------
+// Fill (i, m, p): row p of the (k+1)^2 Fourier polynomials of level m of GGSW i -> slot p & 3.
+template <class C> __device__ __noinline__ void issue_fill(u32 i, u32 m, u32 p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
+  const double2 *bsk = ctrl->bsk;
+  const u32 level = ctrl->level;
+  const u32 slot = p & (C::SLOTS - 1);
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
+  mbar_expect_tx(&ctrl->full_bar[slot], C::FILL_BYTES);
+  const double2 *src = bsk + ((size_t)i * level + m) * C::GS * C::GS * C::M + (size_t)p * C::T;
+  unsigned char *dst = smem + C::OFF_RING + slot * C::FILL_BYTES;
+#pragma unroll
+  for (int poly = 0; poly < C::GS * C::GS; ++poly)
+    tma_load_bulk(dst + poly * C::ROW_BYTES, src + (size_t)poly * C::M, C::ROW_BYTES,
+                  &ctrl->full_bar[slot]);
+}
+
+// This warp has issued its last read of the fill in slot p & 3: count it; the warp that counts
+// last refills the slot with the fill SLOTS ahead (if there is one).
+template <class C>
+__device__ __forceinline__ void fill_done(int lane, u32 i, u32 m, int p, u32 fill) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __syncwarp();
+  if (lane == 0) {
+    const Ctrl *ctrl = reinterpret_cast<const Ctrl *>(smem + C::OFF_CTRL);
+    u32 old;
+    asm volatile("atom.shared.inc.u32 %0, [%1], %2;" // wraps to 0 after the last warp
+                 : "=r"(old)
+                 : "r"(smem_u32(smem) + C::OFF_CTRL + 32 + 4 * (p & (C::SLOTS - 1))),
+                   "n"(C::NWARPS - 1)
+                 : "memory");
+    if (old == (u32)C::NWARPS - 1 && fill + C::SLOTS < ctrl->total_fills) {
+      u32 pn = (u32)p + C::SLOTS, mn = m, in = i;
+      if (pn >= (u32)C::P) {
+        pn -= C::P;
+        if (++mn == ctrl->level) {
+          mn = 0;
+          in = (i + 1 == ctrl->n) ? 0 : i + 1;
+        }
+      }
+      issue_fill<C>(in, mn, pn);
+    }
+  }
+}
+
+template <class C> __device__ __forceinline__ void wait_fill(int p) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
+  mbar_wait(&ctrl->full_bar[p & (C::SLOTS - 1)], (u32)((p / C::SLOTS) & 1));
+}
+
+// a ciphertext slot with nothing to do in this CMUX (idle slot of the last round, or a_hat == 0)
+// still walks the ring: every warp of the CTA consumes every fill
+template <class C>
+__device__ __noinline__ void idle_cmux(u32 i, u32 fill0) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int lane = opaque_tid() & 31;
+  const u32 level = reinterpret_cast<const Ctrl *>(smem + C::OFF_CTRL)->level;
+  for (u32 m = 0; m < level; ++m) {
+#pragma unroll 1
+    for (int p = 0; p < C::P; ++p) {
+      wait_fill<C>(p);
+      fill_done<C>(lane, i, m, p, fill0 + m * C::P + p);
+    }
+  }
+}
+
+__device__ __forceinline__ void unpack4(const u32 (&v)[16], u64 (&re)[4], u64 (&im)[4]) {
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    re[e] = ((u64)v[4 * e + 1] << 32) | v[4 * e + 0];
+    im[e] = ((u64)v[4 * e + 3] << 32) | v[4 * e + 2];
+  }
+}
+__device__ __forceinline__ void pack4(u32 (&v)[16], const u64 (&re)[4], const u64 (&im)[4]) {
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    v[4 * e + 0] = (u32)re[e];
+    v[4 * e + 1] = (u32)(re[e] >> 32);
+    v[4 * e + 2] = (u32)im[e];
+    v[4 * e + 3] = (u32)(im[e] >> 32);
+  }
+}
+
+// One CMUX of polynomial r of one ciphertext (one group).  Out of line on purpose: the caller's
+// loop state (round, sample, LWE pointer) must not stay live across the transforms; everything
+// the body needs beyond its three arguments comes from the thread index or the control block.
+template <class C, bool NARROW, int LV>
+__device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 fill0) {
+  using st_t = typename std::conditional<NARROW, u32, u64>::type;
+  constexpr int P = C::P, T = C::T, M = C::M, N = C::N, LOGM = C::LOGM, GS = C::GS;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const Ctrl *ctrl = reinterpret_cast<const Ctrl *>(smem + C::OFF_CTRL);
+  const double2 *__restrict__ tw = ctrl->tw;
+  const u32 base_log = ctrl->base_log, level = LV ? (u32)LV : ctrl->level;
+
+  // ---- phase A: ct1_r = ACC_r * X^a - ACC_r, rounding, decomposition states
+  st_t st_re[P], st_im[P];
+  {
+    const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5;
+    const ulonglong2 *acc = reinterpret_cast<const ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
+    const u32 tm_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
+                       (u32)(warp >> 2) * C::TM_PER_WARP;
+    const u32 round_shift = 64 - base_log * level - 1;
+    const u32 state_shift = 64 - base_log * level;
+#pragma unroll
+    for (int c4 = 0; c4 < P / 4; ++c4) {
+      u32 v[16];
+      tmem_ld16(tm_own + 16 * c4, v);
+      tmem_wait_ld();
+      u64 own_re[4], own_im[4];
+      unpack4(v, own_re, own_im);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int p = 4 * c4 + e;
+        const int j = t + p * T;
+        const u32 s = (u32)(j - (int)a_hat) & (2 * N - 1);
+        const u32 q = s >> LOGM;
+        const ulonglong2 src = acc[s & (M - 1)];
+        const u64 ra = (q & 1) ? src.y : src.x;
+        const u64 rb = (q & 1) ? src.x : src.y;
+        const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
+        const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
+        st_re[p] = (st_t)(closest_representable(rot_re - own_re[e], round_shift) >> state_shift);
+        st_im[p] = (st_t)(closest_representable(rot_im - own_im[e], round_shift) >> state_shift);
+      }
+    }
+  }
+
+  double2 x[P];
+#pragma unroll 1
+  for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
+    {
+      const st_t mask = (st_t)(((u64)1 << base_log) - 1);
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        x[p].x = __int2double_rn((int)(u32)grp_decompose<st_t>(st_re[p], mask, base_log));
+        x[p].y = __int2double_rn((int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
+      }
+    }
+    forward<C>(x, tw); // its first barrier also ends the rotated reads of ACC
+    {
+      const int tid = opaque_tid(), t = tid % T, grp = tid / T;
+      double2 *buf = reinterpret_cast<double2 *>(smem + (size_t)grp * C::BUF_BYTES);
+      grp_bar<C>(grp); // last exchange fully read
+#pragma unroll
+      for (int p = 0; p < P; ++p) buf[p * T + t] = x[p]; // F_{r,m} parked in key order
+      ct_bar<C>(grp / GS);                               // every F_{.,m} of this ciphertext visible
+    }
+
+    // ---- phase B: column r of the external product, in place in x
+    {
+      const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5, lane = tid & 31;
+      const int ct = grp / GS, r = grp % GS;
+      const u32 tm_stash = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
+                           (u32)(warp >> 2) * C::TM_PER_WARP + C::TM_OWN;
+      const u32 ring = smem_u32(smem) + C::OFF_RING + (u32)t * 16 + (u32)r * C::ROW_BYTES;
+      const u32 sib = smem_u32(smem) + (u32)(ct * GS) * C::BUF_BYTES + (u32)t * 16;
+#pragma unroll
+      for (int c4 = 0; c4 < P / 4; ++c4) {
+        u32 v[16];
+        if (C::STASH && m > 0) {
+          tmem_ld16(tm_stash + 16 * c4, v);
+          tmem_wait_ld();
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int p = 4 * c4 + e;
+          wait_fill<C>(p);
+          const u32 slot = ring + (u32)(p & (C::SLOTS - 1)) * C::FILL_BYTES;
+          double2 o = make_double2(0.0, 0.0);
+          if (C::STASH && m > 0)
+            o = make_double2(__hiloint2double((int)v[4 * e + 1], (int)v[4 * e + 0]),
+                             __hiloint2double((int)v[4 * e + 3], (int)v[4 * e + 2]));
+#pragma unroll
+          for (int rr = 0; rr < GS; ++rr) {
+            double2 w, f;
+            asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                         : "=d"(w.x), "=d"(w.y)
+                         : "r"(slot + (u32)(rr * GS) * C::ROW_BYTES));
+            if (rr == r) {
+              f = x[p];
+            } else {
+              asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                           : "=d"(f.x), "=d"(f.y)
+                           : "r"(sib + (u32)rr * C::BUF_BYTES + (u32)(p * T * 16)));
+            }
+            o.x = fma(f.x, w.x, fma(-f.y, w.y, o.x));
+            o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
+          }
+          x[p] = o;
+          fill_done<C>(lane, i, m, p, fill0 + m * P + p);
+        }
+      }
+      ct_bar<C>(ct); // every read of the parked transforms done before the buffers are reused
+      if (C::STASH && m + 1 < level) {
+#pragma unroll
+        for (int c4 = 0; c4 < P / 4; ++c4) {
+          u32 v[16];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            v[4 * e + 0] = (u32)__double2loint(x[4 * c4 + e].x);
+            v[4 * e + 1] = (u32)__double2hiint(x[4 * c4 + e].x);
+            v[4 * e + 2] = (u32)__double2loint(x[4 * c4 + e].y);
+            v[4 * e + 3] = (u32)__double2hiint(x[4 * c4 + e].y);
+          }
+          tmem_st16(tm_stash + 16 * c4, v);
+        }
+        tmem_wait_st();
+      }
+    }
+  }
+
+  // ---- phase C: inverse transform, torus rounding, ACC += (own copy in TMEM, home in smem)
+  inverse<C>(x, tw);
+  {
+    const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5;
+    ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
+    const u32 tm_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
+                       (u32)(warp >> 2) * C::TM_PER_WARP;
+    grp_bar<C>(grp); // last exchange fully read before the buffer becomes the accumulator again
+#pragma unroll
+    for (int c4 = 0; c4 < P / 4; ++c4) {
+      u32 v[16];
+      tmem_ld16(tm_own + 16 * c4, v);
+      tmem_wait_ld();
+      u64 re[4], im[4];
+      unpack4(v, re, im);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int p = 4 * c4 + e;
+        re[e] += from_torus(x[p].x);
+        im[e] += from_torus(x[p].y);
+        acc[t + p * T] = make_ulonglong2(re[e], im[e]);
+      }
+      pack4(v, re, im);
+      tmem_st16(tm_own + 16 * c4, v);
+    }
+    tmem_wait_st();
+    grp_bar<C>(grp); // ACC_r complete before the rotated reads of the next CMUX
+  }
+}
+
+template <class C, bool NARROW, int LV>
+__global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) {
+  constexpr int P = C::P, T = C::T, M = C::M, N = C::N, GS = C::GS, K = C::K, CPB = C::CPB;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int grp = tid / T, t = tid % T, ct = grp / GS, r = grp % GS;
+  ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
+  Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
+  const u32 n = a.n, level = LV ? (u32)LV : a.level;
+  const size_t out_size = (size_t)K * N + 1;
+
+  // Sample -> (CTA, round, slot), as in pbs_kernel_w32v3: `full` rounds with CPB ciphertexts in
+  // every CTA, then the remainder spread evenly over all CTAs in one last (shorter) round.
+  const u32 wave = gridDim.x * CPB;
+  const u32 full = a.num_samples / wave;
+  const u32 rem = a.num_samples - full * wave;
+  const u32 rem_base = rem / gridDim.x, rem_extra = rem % gridDim.x;
+  const u32 my_rem = rem_base + (blockIdx.x < rem_extra ? 1u : 0u);
+  const u32 rem_first = full * wave + blockIdx.x * rem_base + min(blockIdx.x, rem_extra);
+  const u32 rounds = full + (my_rem ? 1u : 0u);
+  const u32 fills_per_cmux = level * P;
+  const u32 total_fills = rounds * n * fills_per_cmux;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < C::SLOTS; ++s) {
+      mbar_init(&ctrl->full_bar[s], 1);
+      ctrl->done_cnt[s] = 0;
+    }
+    ctrl->n = n;
+    ctrl->level = level;
+    ctrl->base_log = a.base_log;
+    ctrl->total_fills = total_fills;
+    ctrl->bsk = a.bsk;
+    ctrl->tw = a.tw;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     smem_u32(&ctrl->tmem_base)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const u32 tm_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
+                     (u32)(warp >> 2) * C::TM_PER_WARP;
+
+  if (tid == 0) { // prologue: the first SLOTS fills
+    for (u32 p = 0; p < (u32)C::SLOTS && p < total_fills; ++p) issue_fill<C>(0, 0, p);
+  }
+
+  u32 fill0 = 0; // fill index of (current CMUX, level 0, row 0)
+  for (u32 rd = 0; rd < rounds; ++rd) {
+    const bool active = rd < full || (u32)ct < my_rem;
+    const u32 sample = rd < full ? rd * wave + blockIdx.x * CPB + ct : rem_first + ct;
+    const u64 *lwe = a.lwe_in + (active ? a.in_idx[sample] : 0) * (u64)(n + 1);
+
+    if (active) { // ACC_r <- LUT_r * X^(-b_hat)   (polynomial_algorithms.rs:500-539)
+      const u32 b_hat = modulus_switch(__ldg(&lwe[n]), C::LOGN + 1);
+      const u64 *lut = a.lut_vector + a.lut_idx[sample] * (u64)(GS * N) + (size_t)r * N;
+#pragma unroll
+      for (int c4 = 0; c4 < P / 4; ++c4) {
+        u64 re[4], im[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int j = t + (4 * c4 + e) * T;
+          {
+            const u32 u = (j + b_hat) & (2 * N - 1);
+            const u64 w = __ldg(&lut[u & (N - 1)]);
+            re[e] = (u < (u32)N) ? w : (u64)0 - w;
+          }
+          {
+            const u32 u = (j + M + b_hat) & (2 * N - 1);
+            const u64 w = __ldg(&lut[u & (N - 1)]);
+            im[e] = (u < (u32)N) ? w : (u64)0 - w;
+          }
+          acc[j] = make_ulonglong2(re[e], im[e]);
+        }
+        u32 v[16];
+        pack4(v, re, im);
+        tmem_st16(tm_own + 16 * c4, v);
+      }
+      tmem_wait_st();
+    }
+    grp_bar<C>(grp);
+
+    u32 a_next = active ? modulus_switch(__ldg(&lwe[0]), C::LOGN + 1) : 0;
+#pragma unroll 1
+    for (u32 i = 0; i < n; ++i, fill0 += fills_per_cmux) {
+      const u32 a_hat = a_next;
+      if (active && i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), C::LOGN + 1);
+      if (a_hat == 0) // X^0 - 1 = 0: no CMUX (bootstrap.rs:287), or an idle slot
+        idle_cmux<C>(i, fill0);
+      else
+        cmux<C, NARROW, LV>(a_hat, i, fill0);
+    }
+
+    // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride: group c < k
+    // writes mask polynomial c from its own accumulator, group k the body
+    if (active) {
+      for (u32 li = 0; li < a.lut_count; ++li) {
+        const u32 nth = li * a.lut_stride;
+        u64 *out = a.lwe_out + ((size_t)li * a.num_samples + a.out_idx[sample]) * out_size;
+        if (r < K) {
+          for (int j = t; j < N; j += T) {
+            const int src = (j <= (int)nth) ? ((int)nth - j) : (N + (int)nth - j);
+            const ulonglong2 pr = acc[src & (M - 1)];
+            const u64 v = (src < M) ? pr.x : pr.y;
+            out[(size_t)r * N + j] = (j <= (int)nth) ? v : (u64)0 - v;
+          }
+        } else if (t == 0) {
+          const ulonglong2 pr = acc[nth & (M - 1)];
+          out[(size_t)K * N] = (nth < (u32)M) ? pr.x : pr.y;
+        }
+      }
+    }
+    grp_bar<C>(grp);
+  }
+
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(ctrl->tmem_base),
+                 "r"(512u)
+                 : "memory");
+}
+
+// ---- K4 for this layout: dst[p*T + t] = F_{t*P + p} / M, in place, one group per polynomial ----
+template <class C>
+__global__ void __launch_bounds__(C::T) bsk_convert_kernel_v4(double2 *bsk,
+                                                              const double2 *__restrict__ tw,
+                                                              size_t num_polys) {
+  constexpr int P = C::P, T = C::T, M = C::M;
+  const int t = threadIdx.x;
+  for (size_t poly = blockIdx.x; poly < num_polys; poly += gridDim.x) {
+    const u64 *src = reinterpret_cast<const u64 *>(bsk + poly * M);
+    double2 x[P];
+#pragma unroll
+    for (int p = 0; p < P; ++p) {
+      const int j = t + p * T;
+      // convert_forward_torus (fft/mod.rs:201-222): signed value * 2^-64
+      x[p].x = __ll2double_rn((i64)src[j]) * 5.421010862427522170037e-20;
+      x[p].y = __ll2double_rn((i64)src[j + M]) * 5.421010862427522170037e-20;
+    }
+    __syncthreads(); // every read of this polynomial precedes the in-place writes
+    // (the CTA is one group: tid / T == 0, exchange buffer at offset 0, barrier of T threads)
+    forward<C>(x, tw);
+    double2 *dst = bsk + poly * M;
+    const double inv_m = 1.0 / (double)M;
+#pragma unroll
+    for (int p = 0; p < P; ++p) dst[p * T + t] = make_double2(x[p].x * inv_m, x[p].y * inv_m);
+    __syncthreads();
+  }
+}
+
+} // namespace v4

@@ -57,6 +57,8 @@ SIGNATURES = {
         None, [vp, u32, vp, vp, vp, vp, vp, vp, i8p, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
     "concrete_b200_version": (C.c_char_p, []),
     "concrete_b200_kernel_launches": (u64, []),
+    "concrete_b200_set_pbs_plan": (None, [C.c_int]),
+    "concrete_b200_set_ks_plan": (None, [C.c_int]),
 }
 
 # runtime wrapper layer, include/concrete_b200_runtime.h (MLIR memref ABI; host pointers)

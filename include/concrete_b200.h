@@ -191,6 +191,13 @@ void cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
  * used by bench.py to report `gpu_launches`. */
 const char *concrete_b200_version(void);
 uint64_t concrete_b200_kernel_launches(void);
+/* TEST hooks (not in the reference): pin the kernel family so that the tests keep every kernel
+ * covered.  PBS: 0 automatic, 1 first generic kernel, 2 group kernel, 3 cluster kernel, 4 v4
+ * (pbs_v4.cuh) wherever it has the shape; must be set BEFORE the bootstrapping key is converted
+ * (the Fourier key layout belongs to the family).  Keyswitch: 0 automatic, 1 integer pipe, 2 INT8
+ * tensor cores whenever exact. */
+void concrete_b200_set_pbs_plan(int plan);
+void concrete_b200_set_ks_plan(int plan);
 /* FP64 FMA peak probe: `blocks` CTAs x 256 threads x iters x 16 DFMA (32 flop) per thread;
  * bench.py times it with CUDA events for the roofline denominator. */
 void concrete_b200_fp64_peak(void *stream, uint32_t gpu_index, void *scratch, uint32_t blocks,

@@ -273,12 +273,44 @@ def test_pbs_reference_parameter_table(engine, k, N, b, l, sig_glwe):
 
 
 @pytest.mark.parametrize("name,n_small", [("TOY512", None), ("P4", 24), ("P7", 16)])
-def test_pbs_cluster_variant(engine, name, n_small, monkeypatch):
+def test_pbs_cluster_variant(engine, name, n_small):
     """The thread-block-cluster variant of the group kernel (one CTA per GLWE polynomial, Fourier
-    digits exchanged through distributed shared memory; pbs_grp.cuh) is not the default anywhere
-    (measured slower at N = 8192) but must stay correct: same checks as the default path."""
-    monkeypatch.setenv("CONCRETE_B200_FORCE_CLUSTER", "1")
-    _pbs_check(engine, keyset(name, n_override=n_small), 7, 3, use_ks=False)
+    digits exchanged through distributed shared memory; pbs_grp.cuh) is the default only at
+    N = 16384 but must stay correct everywhere: same checks as the default path."""
+    engine.lib.concrete_b200_set_pbs_plan(3)
+    try:
+        _pbs_check(engine, keyset(name, n_override=n_small), 7, 3, use_ks=False)
+    finally:
+        engine.lib.concrete_b200_set_pbs_plan(0)
+
+
+@pytest.mark.parametrize("plan", [1, 2, 4])
+@pytest.mark.parametrize("name,n_small", [("TOY1024", None), ("P2048", 20), ("P4", 24), ("P6", 16),
+                                          ("P7", 12)])
+def test_pbs_every_kernel_family(engine, name, n_small, plan):
+    """Plans 1 (first generic kernel), 2 (group kernel) and 4 (v4: TMEM-resident accumulator copy,
+    TMA key ring) on the shapes where the automatic plan would pick another family."""
+    engine.lib.concrete_b200_set_pbs_plan(plan)
+    try:
+        _pbs_check(engine, keyset(name, n_override=n_small), 11, 3, use_ks=False)
+    finally:
+        engine.lib.concrete_b200_set_pbs_plan(0)
+
+
+@pytest.mark.parametrize("k,N,b,l", [(1, 8192, 15, 2), (1, 1024, 12, 3), (1, 2048, 9, 3),
+                                     (2, 1024, 10, 2), (1, 4096, 11, 2), (1, 2048, 16, 2)])
+def test_pbs_v4_multi_level(engine, k, N, b, l):
+    """v4 with l >= 2: Fourier accumulators parked in tensor memory between levels; 32-bit
+    (b*l <= 31) and 64-bit (b*l > 31) decomposition states."""
+    prm = TfheParams(f"V4_k{k}_N{N}_l{l}", 20, k, N, l, b, 3, 4, 2, 2.0 ** -24, 2.0 ** -55)
+    _pbs_check(engine, KeySet(prm, seed=42), 13, 2, use_ks=False)
+
+
+def test_pbs_v4_rounds_and_tail(engine):
+    """More ciphertexts than one wave of the persistent v4 grid (full rounds + a ragged tail spread
+    over all CTAs) with the small dimension cut so that the oracle finishes in seconds."""
+    ks = keyset("TOY1024", n_override=6)  # k = 1, N = 1024: 8 ciphertexts per CTA
+    _pbs_check(engine, ks, 148 * 8 + 148 * 3 + 17, 3, use_ks=False)
 
 
 def test_pbs_empty_batch(engine):
