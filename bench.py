@@ -68,69 +68,77 @@ def workload_config(p, samples, n_gpus):
 
 
 # --------------------------------------------------------------------------- CPU legs (oracle)
-def cpu_oracle_rate(p, ks, cts_big, lut, budget_s, native=True):
-    """Times the oracle port (KS + PBS) on a bounded sample with all host threads."""
+CPU_NOTE = ("vectorised port oracle/tfhe_fast.cpp (8 ciphertexts per SIMD batch, fused radix-2x2 "
+            "passes, -march=native); concrete-cpu itself (Rust, concrete-fft AVX-512) is "
+            "unavailable on this box (no Rust toolchain)")
+
+
+def cpu_threads():
+    """All host threads, whatever the launcher exported (torchrun sets OMP_NUM_THREADS=1)."""
     import oracle as orc
 
-    try:
-        orc.lib(native=native)
-    except Exception:
-        native = False
-    cores = orc.num_threads(native)
-    # calibrate with one ciphertext per thread
-    cal = cts_big[:cores]
+    want = os.cpu_count() or 1
+    fl = orc.fast_lib()
+    fl.fast_set_num_threads(want)
+    return fl.fast_num_threads(), fl.fast_simd_bits()
+
+
+def cpu_step(p, ks, cts, lut):
+    """One pass of the hot path on the host cores: keyswitch + PBS (timed CPU implementation)."""
+    import oracle as orc
+
+    mid = orc.fast_keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    return orc.fast_bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l)
+
+
+def cpu_oracle_rate(p, ks, cts_big, lut, budget_s):
+    """Times the CPU port (KS + PBS) on a bounded sample with all host threads."""
+    cores, simd = cpu_threads()
+    per_round = cores * 8  # one SIMD batch per thread
+    cal = cts_big[:per_round]
+    cpu_step(p, ks, cal[: max(8, per_round // 4)], lut)  # warm-up (builds the plan, pages in)
     t0 = time.perf_counter()
-    mid = orc.keyswitch(cal, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
-    orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
+    cpu_step(p, ks, cal, lut)
     t_cal = time.perf_counter() - t0
     rounds = max(1, int(budget_s / max(t_cal, 1e-3)))
-    count = min(len(cts_big), cores * rounds)
+    count = min(len(cts_big), per_round * rounds)
     sample = cts_big[:count]
     t0 = time.perf_counter()
-    mid = orc.keyswitch(sample, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
-    out = orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
+    out = cpu_step(p, ks, sample, lut)
     dt = time.perf_counter() - t0
     return {
-        "value": count / dt, "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": f"{count} ciphertexts (KS+PBS, {p.name}) in {dt:.2f} s, OpenMP x{cores}, "
-                  f"{'-march=native' if native else 'x86-64-v3'} build of oracle/tfhe_oracle.cpp",
+        "value": count / dt, "unit": UNIT, "cores": cores, "kind": "port", "simd_bits": simd,
+        "ms_per_pbs_per_thread": dt * 1e3 * cores / count,
+        "sample": f"sampled: {count} ciphertexts (KS+PBS, {p.name}) in {dt:.2f} s, OpenMP "
+                  f"x{cores}; {CPU_NOTE}",
     }, out, count
 
 
 def run_reference(args):
-    """`--impl reference`: the CPU restatement of the reference path (concrete-cpu itself cannot be
-    built here: no Rust toolchain), all host threads, bounded sample per step."""
+    """`--impl reference`: the reference path on the box's host cores (CPU port; concrete-cpu
+    itself cannot be built here), all host threads, a bounded sample per step.  Under torchrun rank
+    0 alone runs and prints; the other ranks exit 0 without work."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     from harness import KeySet, PARAMS, expand_lut, trivial_glwe
-    import oracle as orc
 
     p = PARAMS[args.workload]
     ks = KeySet(p, seed=42)
     bits = min(p.msg_bits, 4)
-    try:
-        orc.lib(native=True)
-        native = True
-    except Exception:
-        native = False
-    cores = orc.num_threads(native)
-    per_step = cores * 2
+    cores, simd = cpu_threads()
+    per_step = cores * 8 * 2
     rng = np.random.default_rng(42)
     msgs = rng.integers(0, 1 << bits, per_step).astype(np.uint64)
     cts = ks.encrypt_big(msgs, bits)
     table = (np.arange(1 << bits) ** 2 % (1 << bits)).astype(np.uint64)
     lut = trivial_glwe(expand_lut(table, p.N, bits), p.k)
 
-    def step():
-        mid = orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks, native=native)
-        return orc.bootstrap(mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l, native=native)
-
     for _ in range(max(1, min(args.warmup, 2))):
-        step()
+        cpu_step(p, ks, cts, lut)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        out = step()
+        out = cpu_step(p, ks, cts, lut)
     dt = time.perf_counter() - t0
     ok = bool(np.array_equal(ks.decrypt_big(out, bits), table[msgs]))
     value = per_step * args.steps / dt
@@ -139,10 +147,14 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64+u64",
         "data": "synthetic (seed 42 keys/ciphertexts)",
-        "config": workload_config(p, args.samples, args.gpus),
+        "config": {**workload_config(p, args.samples, args.gpus),
+                   "sampled": f"{per_step} ciphertexts per step (a bounded sample of the "
+                              f"{args.samples}-ciphertext batch; the rate does not depend on it)"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{per_step} ciphertexts per step (KS+PBS), OpenMP x{cores}; "
-                                   "concrete-cpu itself unavailable (no Rust toolchain)"},
+                         "simd_bits": simd,
+                         "ms_per_pbs_per_thread": dt / args.steps * 1e3 / per_step * cores,
+                         "sample": f"sampled: {per_step} ciphertexts per step (KS+PBS), OpenMP "
+                                   f"x{cores}; {CPU_NOTE}"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "verified_decryptions": ok,
     }

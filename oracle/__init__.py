@@ -83,6 +83,46 @@ def lib(native: bool = False):
     return l
 
 
+_FAST = None
+
+
+def fast_lib():
+    """The vectorised timed baseline (oracle/tfhe_fast.cpp), -march=native, built where it runs."""
+    global _FAST
+    if _FAST is not None:
+        return _FAST
+    name = _native_name().replace("liboracle_native", "libfast_native")
+    path = os.path.join(_HERE, name)
+    src = os.path.join(_HERE, "tfhe_fast.cpp")
+    if not os.path.exists(path) or os.path.getmtime(src) > os.path.getmtime(path):
+        subprocess.run(["make", "-C", _HERE, "fast", f"FAST_SO={name}"], check=True,
+                       capture_output=True)
+    l = C.CDLL(path)
+    l.fast_num_threads.restype = C.c_int
+    l.fast_set_num_threads.argtypes = [C.c_int]
+    l.fast_simd_bits.restype = C.c_int
+    _FAST = l
+    return l
+
+
+def fast_keyswitch(cts, ksk, n_in, n_out, base_log, level) -> np.ndarray:
+    num = cts.shape[0]
+    out = np.empty((num, n_out + 1), dtype=np.uint64)
+    fast_lib().fast_keyswitch_batch(_p(out), _p(cts), _p(ksk), n_in, n_out, base_log, level,
+                                    C.c_size_t(num))
+    return out
+
+
+def fast_bootstrap(cts, luts, lut_idx, fbsk, n, k, N, base_log, level) -> np.ndarray:
+    num = cts.shape[0]
+    luts = np.ascontiguousarray(luts.reshape(-1, (k + 1) * N))
+    out = np.empty((num, k * N + 1), dtype=np.uint64)
+    idx = None if lut_idx is None else _p(np.ascontiguousarray(lut_idx, dtype=np.uint64))
+    fast_lib().fast_bootstrap_batch(_p(out), _p(cts), _p(luts), idx, _p(fbsk, np.complex128), n, k,
+                                    C.c_size_t(N), base_log, level, C.c_size_t(num))
+    return out
+
+
 def _p(a: np.ndarray, dtype=np.uint64):
     assert a.dtype == dtype and a.flags["C_CONTIGUOUS"], (a.dtype, a.flags)
     return a.ctypes.data_as(C.c_void_p)

@@ -258,3 +258,26 @@ def test_encode_decode_and_lut_expansion():
     # wrappers.cpp:388-450: half a mega-case of table[0] first, negated table[0] at the end
     assert lut[0] == 0 and lut[4] == np.uint64(1) << np.uint64(61)
     assert lut[3] == 0 and lut[12] == np.uint64(2) << np.uint64(61)
+
+
+@pytest.mark.parametrize("name,bits,num", [("TOY512", 3, 21), ("TOY256K2", 2, 9), ("TOY1024", 3, 17)])
+def test_timed_cpu_baseline_agrees_with_the_oracle(name, bits, num):
+    """oracle/tfhe_fast.cpp (the vectorised CPU implementation bench.py TIMES) against the scalar
+    oracle (the CHECKER): keyswitch words equal, PBS decryptions equal, PBS phases within the
+    tolerance two f64 implementations can be held to (harness.phase_tolerance).  Includes a zero
+    mask element (skipped CMUX) and a ragged last SIMD batch."""
+    from harness import phase_distance, phase_tolerance
+
+    ks = KeySet(PARAMS[name], seed=42)
+    p = ks.p
+    msgs = (np.arange(num) % (1 << bits)).astype(np.uint64)
+    cts = ks.encrypt_big(msgs, bits, seed=3)
+    ref_mid = orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    assert np.array_equal(orc.fast_keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks), ref_mid)
+    ref_mid[2, 1] = 0
+    table = ((np.arange(1 << bits) * 3 + 1) % (1 << bits)).astype(np.uint64)
+    lut = trivial_glwe(expand_lut(table, p.N, bits), p.k)
+    ref = orc.bootstrap(ref_mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l)
+    got = orc.fast_bootstrap(ref_mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l)
+    assert np.array_equal(ks.decrypt_big(got, bits), ks.decrypt_big(ref, bits))
+    assert phase_distance(ks, got, ref).max() <= phase_tolerance(p)
