@@ -16,9 +16,9 @@ struct V4Variant {
   size_t smem, smem_stash, convert_smem;
 };
 
-template <int K, int LOGN, int CPB> V4Variant make_v4() {
-  using C1 = v4::Cfg<K, LOGN, 4, CPB, false>;
-  using CL = v4::Cfg<K, LOGN, 4, CPB, true>;
+template <int K, int LOGN, int CPB, int RB, int NB> V4Variant make_v4() {
+  using C1 = v4::Cfg<K, LOGN, 4, CPB, false, RB, NB>;
+  using CL = v4::Cfg<K, LOGN, 4, CPB, true, RB, NB>;
   V4Variant v;
   v.one_level = v4::pbs_kernel_v4<C1, true, 1>;
   v.multi_narrow = v4::pbs_kernel_v4<CL, true, 0>;
@@ -38,11 +38,13 @@ template <int K, int LOGN, int CPB> V4Variant make_v4() {
 // (k = 2, N = 1024).  N = 16384 needs the two polynomials of a ciphertext on two SMs (256 KiB of
 // accumulator): see pbs_v4 cluster notes in DESIGN.md.
 bool v4_variant(u32 k, u32 N, V4Variant &v) {
-  if (k == 1 && N == 1024) { v = make_v4<1, 10, 8>(); return true; }
-  if (k == 1 && N == 2048) { v = make_v4<1, 11, 4>(); return true; }
-  if (k == 1 && N == 4096) { v = make_v4<1, 12, 2>(); return true; }
-  if (k == 1 && N == 8192) { v = make_v4<1, 13, 1>(); return true; }
-  if (k == 2 && N == 1024) { v = make_v4<2, 10, 5>(); return true; }
+  // <k, log2 N, ciphertexts per CTA, rows per ring block, ring blocks>: RB * NB of the 16 rows of a
+  // GGSW level are resident; the whole level where the shared memory left by the buffers allows
+  if (k == 1 && N == 1024) { v = make_v4<1, 10, 8, 8, 2>(); return true; }  // 128 + 32 KiB
+  if (k == 1 && N == 2048) { v = make_v4<1, 11, 4, 8, 2>(); return true; }  // 128 + 64 KiB
+  if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
+  if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
+  if (k == 2 && N == 1024) { v = make_v4<2, 10, 5, 8, 2>(); return true; }  // 120 + 72 KiB
   return false;
 }
 

@@ -15,10 +15,9 @@
 //   * the thread's own accumulator pairs live in TENSOR MEMORY (tcgen05.ld/st 32x32b), which is
 //     what makes that aliasing possible; for l >= 2 the Fourier accumulators are parked there too
 //     during the next level's forward transform (no spills, no global-memory accumulator);
-//   * the Fourier GGSW streams through a 4-slot shared-memory ring by bulk TMA copies
-//     (cp.async.bulk + mbarrier complete_tx), one fill = row p (of P) of the (k+1)^2 polynomials
-//     of one level, shared by every ciphertext of the CTA; slot and parity of a fill are
-//     compile-time constants (P fills per level = a whole even number of ring revolutions);
+//   * the Fourier GGSW streams through a shared-memory ring by bulk TMA copies (cp.async.bulk +
+//     mbarrier complete_tx) in blocks of RB rows (row p = the points {t*P + p} of the (k+1)^2
+//     polynomials of one level), shared by every ciphertext of the CTA;
 //   * exchanges are XOR-swizzled (conflict-free for every pass pattern), the key and the parked
 //     transform are stored [p][t] (conflict-free LDS.128).
 // Arithmetic: identical to pbs_kernel / pbs_kernel_grp (same rounding, same transforms, same
@@ -28,7 +27,7 @@
 namespace v4 {
 using namespace sm100;
 
-template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_> struct Cfg {
+template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int NB_ = 2> struct Cfg {
   static constexpr int K = K_, LOGN = LOGN_, LOGM = LOGN_ - 1, M = 1 << LOGM, N = 2 * M;
   static constexpr int LOGP = LOGP_, P = 1 << LOGP_, T = M / P;
   static constexpr int GS = K_ + 1, CPB = CPB_, GROUPS = CPB_ * GS, THREADS = GROUPS * T;
@@ -36,27 +35,33 @@ template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_> struct Cfg {
   static constexpr bool STASH = STASH_; // l >= 2: Fourier accumulators parked in TMEM
   static constexpr u32 BUF_BYTES = (u32)M * 16;
   static constexpr u32 ROW_BYTES = (u32)T * 16;               // row p of one key polynomial
-  static constexpr u32 FILL_BYTES = (u32)GS * GS * ROW_BYTES; // row p of one GGSW level
-  static constexpr int SLOTS = 4;
+  // Key ring: NB blocks of RB rows (row p = the T points {t*P + p} of every polynomial of one GGSW
+  // level).  One mbarrier wait and one completion count per BLOCK, not per row: a try_wait costs
+  // ~90 cycles even when the data is there and the count is an atomic round trip, and with one of
+  // each per row they were the critical path of the product (profiles/r2_v4a_*).  RB * NB rows is
+  // what the shared memory left by the buffers holds: the whole level when it fits.
+  static constexpr int RB = RB_, NB = NB_, BLOCKS_PER_LEVEL = P / RB_;
+  static constexpr u32 POLY_BLOCK_BYTES = (u32)RB_ * ROW_BYTES;         // RB rows of one polynomial
+  static constexpr u32 BLOCK_BYTES = (u32)GS * GS * POLY_BLOCK_BYTES;   // RB rows of one level
   static constexpr u32 OFF_RING = (u32)GROUPS * BUF_BYTES;
-  static constexpr u32 OFF_CTRL = OFF_RING + SLOTS * FILL_BYTES;
-  static constexpr size_t SMEM = (size_t)OFF_CTRL + 128;
+  static constexpr u32 OFF_CTRL = OFF_RING + NB_ * BLOCK_BYTES;
+  static constexpr size_t SMEM = (size_t)OFF_CTRL + 256;
   static constexpr u32 TM_OWN = 4 * P;                           // columns of a thread's own pairs
   static constexpr u32 TM_PER_WARP = TM_OWN * (STASH_ ? 2 : 1);
   static constexpr int NPASS = (LOGM + LOGP - 1) / LOGP;
   static_assert(T >= 32 && T % 32 == 0, "a group is a whole number of warps");
   static_assert(THREADS <= 1024 && THREADS % 32 == 0, "CTA size");
   static_assert(((NWARPS + 3) / 4) * TM_PER_WARP <= 512, "TMEM columns");
-  static_assert((P / SLOTS) % 2 == 0, "static mbarrier parity needs an even number of revolutions");
+  static_assert(P % RB_ == 0 && NB_ >= 1 && NB_ <= 16, "ring shape");
   static_assert(SMEM <= 232448, "shared memory");
   static_assert(T == 32 || CPB_ + GROUPS <= 15, "named barriers");
 };
 
 struct Ctrl {
-  unsigned long long full_bar[4];
-  unsigned int done_cnt[4];
+  unsigned long long full_bar[16];
+  unsigned int done_cnt[16];
   unsigned int tmem_base;
-  unsigned int n, level, base_log, total_fills;
+  unsigned int n, level, base_log, total_blocks;
   const double2 *bsk, *tw;
 };
 
@@ -193,27 +198,62 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
 }
 
 // ---- key ring -----------------------------------------------------------------------------------
-// Fill (i, m, p): row p of the (k+1)^2 Fourier polynomials of level m of GGSW i -> slot p & 3.
-template <class C> __device__ __noinline__ void issue_fill(u32 i, u32 m, u32 p) {
+// Block number `blk` (counted from the start of the kernel) = rows [b*RB, (b+1)*RB) of the
+// (k+1)^2 Fourier polynomials of level m of GGSW i -> slot blk % NB.  The RB rows of one
+// polynomial are contiguous in the key (layout [p][t]): one bulk copy per polynomial.
+template <class C> __device__ __noinline__ void issue_block(u32 i, u32 m, u32 b, u32 slot) {
   extern __shared__ __align__(1024) unsigned char smem[];
   Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
   const double2 *bsk = ctrl->bsk;
   const u32 level = ctrl->level;
-  const u32 slot = p & (C::SLOTS - 1);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
-  mbar_expect_tx(&ctrl->full_bar[slot], C::FILL_BYTES);
-  const double2 *src = bsk + ((size_t)i * level + m) * C::GS * C::GS * C::M + (size_t)p * C::T;
-  unsigned char *dst = smem + C::OFF_RING + slot * C::FILL_BYTES;
+  mbar_expect_tx(&ctrl->full_bar[slot], C::BLOCK_BYTES);
+  const double2 *src =
+      bsk + ((size_t)i * level + m) * C::GS * C::GS * C::M + (size_t)b * C::RB * C::T;
+  unsigned char *dst = smem + C::OFF_RING + slot * C::BLOCK_BYTES;
 #pragma unroll
   for (int poly = 0; poly < C::GS * C::GS; ++poly)
-    tma_load_bulk(dst + poly * C::ROW_BYTES, src + (size_t)poly * C::M, C::ROW_BYTES,
+    tma_load_bulk(dst + poly * C::POLY_BLOCK_BYTES, src + (size_t)poly * C::M, C::POLY_BLOCK_BYTES,
                   &ctrl->full_bar[slot]);
+  // Keys that do not fit the 126 MB L2 (N >= 4096: 115 MB .. 240 MB): all CTAs walk the GGSW index
+  // together, so ONE early request per block turns every later fill into an L2 hit.  An eighth of
+  // the CTAs asks for the same block two GGSWs ahead.
+  if (C::LOGN >= 12 && (blockIdx.x & 7u) == (b & 7u) && i + 2 < ctrl->n) {
+    const double2 *ahead = src + (size_t)2 * level * C::GS * C::GS * C::M;
+#pragma unroll
+    for (int poly = 0; poly < C::GS * C::GS; ++poly)
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ahead + (size_t)poly * C::M),
+                   "n"(C::POLY_BLOCK_BYTES)
+                   : "memory");
+  }
 }
 
-// This warp has issued its last read of the fill in slot p & 3: count it; the warp that counts
-// last refills the slot with the fill SLOTS ahead (if there is one).
+// (slot, parity) of a block: slot = blk % NB, parity = (blk / NB) & 1
+struct RingPos {
+  u32 slot, parity;
+};
+template <class C> __device__ __forceinline__ RingPos ring_pos(u32 blk) {
+  RingPos r;
+  r.slot = blk % (u32)C::NB;
+  r.parity = (blk / (u32)C::NB) & 1u;
+  return r;
+}
+template <class C> __device__ __forceinline__ void ring_next(RingPos &r) {
+  if (++r.slot == (u32)C::NB) {
+    r.slot = 0;
+    r.parity ^= 1u;
+  }
+}
+template <class C> __device__ __forceinline__ void wait_block(const RingPos &r) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
+  mbar_wait(&ctrl->full_bar[r.slot], r.parity);
+}
+
+// This warp has issued its last read of block `blk` (level m, index b in the level): count it;
+// the warp that counts last refills the slot with the block NB ahead (if there is one).
 template <class C>
-__device__ __forceinline__ void fill_done(int lane, u32 i, u32 m, int p, u32 fill) {
+__device__ __forceinline__ void block_done(int lane, u32 i, u32 m, u32 b, u32 blk, u32 slot) {
   extern __shared__ __align__(1024) unsigned char smem[];
   __syncwarp();
   if (lane == 0) {
@@ -221,41 +261,36 @@ __device__ __forceinline__ void fill_done(int lane, u32 i, u32 m, int p, u32 fil
     u32 old;
     asm volatile("atom.shared.inc.u32 %0, [%1], %2;" // wraps to 0 after the last warp
                  : "=r"(old)
-                 : "r"(smem_u32(smem) + C::OFF_CTRL + 32 + 4 * (p & (C::SLOTS - 1))),
-                   "n"(C::NWARPS - 1)
+                 : "r"(smem_u32(smem) + C::OFF_CTRL + 128 + 4 * slot), "n"(C::NWARPS - 1)
                  : "memory");
-    if (old == (u32)C::NWARPS - 1 && fill + C::SLOTS < ctrl->total_fills) {
-      u32 pn = (u32)p + C::SLOTS, mn = m, in = i;
-      if (pn >= (u32)C::P) {
-        pn -= C::P;
+    if (old == (u32)C::NWARPS - 1 && blk + C::NB < ctrl->total_blocks) {
+      u32 bn = b + C::NB, mn = m, in = i;
+      while (bn >= (u32)C::BLOCKS_PER_LEVEL) {
+        bn -= C::BLOCKS_PER_LEVEL;
         if (++mn == ctrl->level) {
           mn = 0;
-          in = (i + 1 == ctrl->n) ? 0 : i + 1;
+          in = (in + 1 == ctrl->n) ? 0 : in + 1;
         }
       }
-      issue_fill<C>(in, mn, pn);
+      issue_block<C>(in, mn, bn, slot);
     }
   }
 }
 
-template <class C> __device__ __forceinline__ void wait_fill(int p) {
-  extern __shared__ __align__(1024) unsigned char smem[];
-  Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
-  mbar_wait(&ctrl->full_bar[p & (C::SLOTS - 1)], (u32)((p / C::SLOTS) & 1));
-}
-
 // a ciphertext slot with nothing to do in this CMUX (idle slot of the last round, or a_hat == 0)
-// still walks the ring: every warp of the CTA consumes every fill
-template <class C>
-__device__ __noinline__ void idle_cmux(u32 i, u32 fill0) {
+// still walks the ring: every warp of the CTA consumes every block
+template <class C> __device__ __noinline__ void idle_cmux(u32 i, u32 blk0) {
   extern __shared__ __align__(1024) unsigned char smem[];
   const int lane = opaque_tid() & 31;
   const u32 level = reinterpret_cast<const Ctrl *>(smem + C::OFF_CTRL)->level;
+  RingPos rp = ring_pos<C>(blk0);
+  u32 blk = blk0;
   for (u32 m = 0; m < level; ++m) {
 #pragma unroll 1
-    for (int p = 0; p < C::P; ++p) {
-      wait_fill<C>(p);
-      fill_done<C>(lane, i, m, p, fill0 + m * C::P + p);
+    for (u32 b = 0; b < (u32)C::BLOCKS_PER_LEVEL; ++b, ++blk) {
+      wait_block<C>(rp);
+      block_done<C>(lane, i, m, b, blk, rp.slot);
+      ring_next<C>(rp);
     }
   }
 }
@@ -281,7 +316,7 @@ __device__ __forceinline__ void pack4(u32 (&v)[16], const u64 (&re)[4], const u6
 // loop state (round, sample, LWE pointer) must not stay live across the transforms; everything
 // the body needs beyond its three arguments comes from the thread index or the control block.
 template <class C, bool NARROW, int LV>
-__device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 fill0) {
+__device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) {
   using st_t = typename std::conditional<NARROW, u32, u64>::type;
   constexpr int P = C::P, T = C::T, M = C::M, N = C::N, LOGM = C::LOGM, GS = C::GS;
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -349,30 +384,34 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 fill0)
       const int ct = grp / GS, r = grp % GS;
       const u32 tm_stash = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
                            (u32)(warp >> 2) * C::TM_PER_WARP + C::TM_OWN;
-      const u32 ring = smem_u32(smem) + C::OFF_RING + (u32)t * 16 + (u32)r * C::ROW_BYTES;
+      const u32 ring = smem_u32(smem) + C::OFF_RING + (u32)t * 16 + (u32)r * C::POLY_BLOCK_BYTES;
       const u32 sib = smem_u32(smem) + (u32)(ct * GS) * C::BUF_BYTES + (u32)t * 16;
+      u32 blk = blk0 + m * C::BLOCKS_PER_LEVEL;
+      RingPos rp = ring_pos<C>(blk);
 #pragma unroll
-      for (int c4 = 0; c4 < P / 4; ++c4) {
-        u32 v[16];
-        if (C::STASH && m > 0) {
-          tmem_ld16(tm_stash + 16 * c4, v);
-          tmem_wait_ld();
-        }
+      for (int b = 0; b < C::BLOCKS_PER_LEVEL; ++b, ++blk) {
+        wait_block<C>(rp);
+        const u32 slot = ring + rp.slot * C::BLOCK_BYTES;
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const int p = 4 * c4 + e;
-          wait_fill<C>(p);
-          const u32 slot = ring + (u32)(p & (C::SLOTS - 1)) * C::FILL_BYTES;
+        for (int pr = 0; pr < C::RB; ++pr) {
+          const int p = b * C::RB + pr;
           double2 o = make_double2(0.0, 0.0);
-          if (C::STASH && m > 0)
-            o = make_double2(__hiloint2double((int)v[4 * e + 1], (int)v[4 * e + 0]),
-                             __hiloint2double((int)v[4 * e + 3], (int)v[4 * e + 2]));
+          if (C::STASH && m > 0) {
+            u32 v[4];
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+                         : "r"(tm_stash + 4 * p)
+                         : "memory");
+            tmem_wait_ld();
+            o = make_double2(__hiloint2double((int)v[1], (int)v[0]),
+                             __hiloint2double((int)v[3], (int)v[2]));
+          }
 #pragma unroll
           for (int rr = 0; rr < GS; ++rr) {
             double2 w, f;
             asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
                          : "=d"(w.x), "=d"(w.y)
-                         : "r"(slot + (u32)(rr * GS) * C::ROW_BYTES));
+                         : "r"(slot + (u32)(rr * GS) * C::POLY_BLOCK_BYTES + (u32)pr * C::ROW_BYTES));
             if (rr == r) {
               f = x[p];
             } else {
@@ -384,8 +423,9 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 fill0)
             o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
           }
           x[p] = o;
-          fill_done<C>(lane, i, m, p, fill0 + m * P + p);
         }
+        block_done<C>(lane, i, m, (u32)b, blk, rp.slot);
+        ring_next<C>(rp);
       }
       ct_bar<C>(ct); // every read of the parked transforms done before the buffers are reused
       if (C::STASH && m + 1 < level) {
@@ -456,19 +496,19 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
   const u32 my_rem = rem_base + (blockIdx.x < rem_extra ? 1u : 0u);
   const u32 rem_first = full * wave + blockIdx.x * rem_base + min(blockIdx.x, rem_extra);
   const u32 rounds = full + (my_rem ? 1u : 0u);
-  const u32 fills_per_cmux = level * P;
-  const u32 total_fills = rounds * n * fills_per_cmux;
+  const u32 blocks_per_cmux = level * C::BLOCKS_PER_LEVEL;
+  const u32 total_blocks = rounds * n * blocks_per_cmux;
 
   if (tid == 0) {
 #pragma unroll
-    for (int s = 0; s < C::SLOTS; ++s) {
+    for (int s = 0; s < C::NB; ++s) {
       mbar_init(&ctrl->full_bar[s], 1);
       ctrl->done_cnt[s] = 0;
     }
     ctrl->n = n;
     ctrl->level = level;
     ctrl->base_log = a.base_log;
-    ctrl->total_fills = total_fills;
+    ctrl->total_blocks = total_blocks;
     ctrl->bsk = a.bsk;
     ctrl->tw = a.tw;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -486,11 +526,13 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
   const u32 tm_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
                      (u32)(warp >> 2) * C::TM_PER_WARP;
 
-  if (tid == 0) { // prologue: the first SLOTS fills
-    for (u32 p = 0; p < (u32)C::SLOTS && p < total_fills; ++p) issue_fill<C>(0, 0, p);
+  if (tid == 0) { // prologue: the first NB blocks
+    for (u32 f = 0; f < (u32)C::NB && f < total_blocks; ++f)
+      issue_block<C>((f / C::BLOCKS_PER_LEVEL) / level, (f / C::BLOCKS_PER_LEVEL) % level,
+                     f % C::BLOCKS_PER_LEVEL, f);
   }
 
-  u32 fill0 = 0; // fill index of (current CMUX, level 0, row 0)
+  u32 blk0 = 0; // block number of (current CMUX, level 0, block 0)
   for (u32 rd = 0; rd < rounds; ++rd) {
     const bool active = rd < full || (u32)ct < my_rem;
     const u32 sample = rd < full ? rd * wave + blockIdx.x * CPB + ct : rem_first + ct;
@@ -527,13 +569,13 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
 
     u32 a_next = active ? modulus_switch(__ldg(&lwe[0]), C::LOGN + 1) : 0;
 #pragma unroll 1
-    for (u32 i = 0; i < n; ++i, fill0 += fills_per_cmux) {
+    for (u32 i = 0; i < n; ++i, blk0 += blocks_per_cmux) {
       const u32 a_hat = a_next;
       if (active && i + 1 < n) a_next = modulus_switch(__ldg(&lwe[i + 1]), C::LOGN + 1);
       if (a_hat == 0) // X^0 - 1 = 0: no CMUX (bootstrap.rs:287), or an idle slot
-        idle_cmux<C>(i, fill0);
+        idle_cmux<C>(i, blk0);
       else
-        cmux<C, NARROW, LV>(a_hat, i, fill0);
+        cmux<C, NARROW, LV>(a_hat, i, blk0);
     }
 
     // sample extraction (glwe_sample_extraction.rs:90-165) at nth = li*lut_stride: group c < k

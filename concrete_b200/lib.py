@@ -84,6 +84,43 @@ SIGNATURES.update({
     "concrete_b200_fp64_peak": (None, [vp, u32, vp, u32, u32]),
 })
 
+# SDFG ("stream emulator") code-generation interface, include/concrete_b200_runtime.h
+# (stream_emulator_api.h:29-104 of the reference)
+_p4 = [vp, vp, vp, vp]
+_ks = [vp, vp, vp, u32, u32, u32, u32, u32, u32, vp]
+_bs = [vp, vp, vp, vp, u32, u32, u32, u32, u32, u32, u32, vp]
+SIGNATURES.update({
+    "stream_emulator_init": (vp, []),
+    "stream_emulator_run": (None, [vp]),
+    "stream_emulator_delete": (None, [vp]),
+    "stream_emulator_make_memref_add_lwe_ciphertexts_u64_process": (None, _p4),
+    "stream_emulator_make_memref_add_plaintext_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_mul_cleartext_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_negate_lwe_ciphertext_u64_process": (None, [vp, vp, vp]),
+    "stream_emulator_make_memref_keyswitch_lwe_u64_process": (None, _ks),
+    "stream_emulator_make_memref_bootstrap_lwe_u64_process": (None, _bs),
+    "stream_emulator_make_memref_batched_add_lwe_ciphertexts_u64_process": (None, _p4),
+    "stream_emulator_make_memref_batched_add_plaintext_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_batched_add_plaintext_cst_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_batched_mul_cleartext_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_batched_mul_cleartext_cst_lwe_ciphertext_u64_process": (None, _p4),
+    "stream_emulator_make_memref_batched_negate_lwe_ciphertext_u64_process": (None, [vp, vp, vp]),
+    "stream_emulator_make_memref_batched_keyswitch_lwe_u64_process": (None, _ks),
+    "stream_emulator_make_memref_batched_bootstrap_lwe_u64_process": (None, _bs),
+    "stream_emulator_make_memref_batched_mapped_bootstrap_lwe_u64_process": (None, _bs),
+    "stream_emulator_make_uint64_stream": (vp, [C.c_char_p, C.c_int]),
+    "stream_emulator_put_uint64": (None, [vp, u64]),
+    "stream_emulator_get_uint64": (u64, [vp]),
+    "stream_emulator_make_memref_stream": (vp, [C.c_char_p, C.c_int]),
+    "stream_emulator_put_memref": (None, [vp, vp, vp, u64, u64, u64, u64]),
+    "stream_emulator_get_memref": (None, [vp, vp, vp, u64, u64, u64]),
+    "stream_emulator_make_memref_batch_stream": (vp, [C.c_char_p, C.c_int]),
+    "stream_emulator_put_memref_batch": (None, [vp, vp, vp, u64, u64, u64, u64, u64, u64]),
+    "stream_emulator_get_memref_batch": (None, [vp, vp, vp, u64, u64, u64, u64, u64]),
+    "concrete_b200_sdfg_set_num_gpus": (None, [vp, C.c_int]),
+    "concrete_b200_sdfg_delete_stream": (None, [vp]),
+})
+
 
 def library_path() -> str:
     return os.path.join(_HERE, "libconcrete_b200.so")
