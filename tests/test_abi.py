@@ -9,13 +9,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def _declared_symbols():
     names = []
-    for hdr in ("concrete_b200.h", "concrete_b200_runtime.h"):
+    for hdr in ("concrete_b200.h", "concrete_b200_runtime.h", "concrete_b200_sdfg.h"):
         text = open(os.path.join(ROOT, "include", hdr)).read()
         text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
         text = re.sub(r"//[^\n]*", "", text)
         for m in re.finditer(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\(", text):
             name = m.group(1)
-            if name.startswith(("cuda_", "scratch_", "cleanup_", "memref_", "concrete_b200_")):
+            if name.startswith(("cuda_", "scratch_", "cleanup_", "memref_", "concrete_b200_", "stream_emulator_")):
                 names.append(name)
     return sorted(set(names))
 
@@ -37,6 +37,34 @@ def test_headers_declare_the_reference_entry_points():
         "memref_batched_bootstrap_lwe_cuda_u64",
         "memref_batched_mapped_bootstrap_lwe_cuda_u64",
         "cuda_add_lwe_ciphertext_vector_64",
+        # the SDFG code-generation interface (stream_emulator_api.h:29-104)
+        "stream_emulator_init",
+        "stream_emulator_run",
+        "stream_emulator_delete",
+        "stream_emulator_make_memref_add_lwe_ciphertexts_u64_process",
+        "stream_emulator_make_memref_add_plaintext_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_mul_cleartext_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_negate_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_keyswitch_lwe_u64_process",
+        "stream_emulator_make_memref_bootstrap_lwe_u64_process",
+        "stream_emulator_make_memref_batched_add_lwe_ciphertexts_u64_process",
+        "stream_emulator_make_memref_batched_add_plaintext_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_batched_add_plaintext_cst_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_batched_mul_cleartext_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_batched_mul_cleartext_cst_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_batched_negate_lwe_ciphertext_u64_process",
+        "stream_emulator_make_memref_batched_keyswitch_lwe_u64_process",
+        "stream_emulator_make_memref_batched_bootstrap_lwe_u64_process",
+        "stream_emulator_make_memref_batched_mapped_bootstrap_lwe_u64_process",
+        "stream_emulator_make_uint64_stream",
+        "stream_emulator_put_uint64",
+        "stream_emulator_get_uint64",
+        "stream_emulator_make_memref_stream",
+        "stream_emulator_put_memref",
+        "stream_emulator_get_memref",
+        "stream_emulator_make_memref_batch_stream",
+        "stream_emulator_put_memref_batch",
+        "stream_emulator_get_memref_batch",
     ):
         assert required in names, required
 
@@ -63,7 +91,7 @@ def test_argument_counts_match_the_headers():
     """Arity of each ctypes prototype equals the number of parameters in the header."""
     from concrete_b200.lib import SIGNATURES
 
-    for hdr in ("concrete_b200.h", "concrete_b200_runtime.h"):
+    for hdr in ("concrete_b200.h", "concrete_b200_runtime.h", "concrete_b200_sdfg.h"):
         text = open(os.path.join(ROOT, "include", hdr)).read()
         text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
         for m in re.finditer(r"\b([A-Za-z_][A-Za-z0-9_]*)\s*\(([^;{]*?)\)\s*;", text, flags=re.S):
