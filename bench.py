@@ -51,6 +51,11 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true",
                     help="skip timing the reference's own GPU library (oracle/_ref witness)")
+    ap.add_argument("--no-configs", action="store_true",
+                    help="skip the short timed legs for the other BASELINE.json configs")
+    ap.add_argument("--no-inlib", action="store_true",
+                    help="skip the one-process leg that shards a batch over all GPUs inside the library")
+    ap.add_argument("--config-steps", type=int, default=2, help="timed steps of every configs leg")
     return ap.parse_args()
 
 
@@ -204,6 +209,233 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(sm) if sm else None,
                 "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
                 "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------- configs legs
+def _events_ms(fn, warmup, steps):
+    """Average device time of fn() over `steps` calls after `warmup` untimed ones (CUDA events on
+    torch's current stream, which is the stream every library call is launched on)."""
+    import torch
+
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(steps):
+        fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / steps
+
+
+class KeyCache:
+    """Seeded key material per parameter set: host keys + device copies (KSK raw, BSK Fourier)."""
+
+    def __init__(self, eng):
+        self.eng, self.ent = eng, {}
+
+    def get(self, name):
+        from harness import KeySet, PARAMS
+
+        if name not in self.ent:
+            p = PARAMS[name]
+            ks = KeySet(p, seed=42, fourier_oracle=False)
+            self.ent[name] = (ks, self.eng.upload_ksk(ks.ksk),
+                              self.eng.convert_bsk(ks.bsk, p.n, p.k, p.l, p.N))
+        return self.ent[name]
+
+    def drop(self, name):
+        self.ent.pop(name, None)
+
+
+def _dev_ops(eng):
+    """The leveled device ops of the C ABI (linear_algebra.h:15-47) as small closures."""
+    import torch
+
+    lib = eng.lib
+
+    def add(a, b, dim, out=None):
+        out = torch.empty_like(a) if out is None else out
+        lib.cuda_add_lwe_ciphertext_vector_64(eng.stream, eng.gpu, out.data_ptr(), a.data_ptr(),
+                                              b.data_ptr(), dim, a.shape[0])
+        return out
+
+    def mul_clear(a, d_clear, dim, out=None):
+        out = torch.empty_like(a) if out is None else out
+        lib.cuda_mult_lwe_ciphertext_vector_cleartext_vector_64(
+            eng.stream, eng.gpu, out.data_ptr(), a.data_ptr(), d_clear.data_ptr(), dim, a.shape[0])
+        return out
+
+    def add_plain(a, d_plain, dim, out=None):
+        out = torch.empty_like(a) if out is None else out
+        lib.cuda_add_lwe_ciphertext_vector_plaintext_vector_64(
+            eng.stream, eng.gpu, out.data_ptr(), a.data_ptr(), d_plain.data_ptr(), dim, a.shape[0])
+        return out
+
+    return add, mul_clear, add_plain
+
+
+def _frac(p, S, pbs_ms, fp64_peak):
+    tf = S * p.pbs_flops() / (pbs_ms * 1e-3) / 1e12
+    return {"bound": "fp64", "achieved": tf, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": tf / fp64_peak, "launch_ms": pbs_ms}
+
+
+def leg_ks_pbs(eng, kc, name, S, steps, fp64_peak, rank, label):
+    """configs[0] / configs[2]: one keyswitch + PBS pass over S ciphertexts of parameter set `name`."""
+    import torch
+    from concrete_b200 import as_u64
+    from harness import expand_lut, trivial_glwe
+
+    ks, d_ksk, d_fbsk = kc.get(name)
+    p = ks.p
+    bits = min(p.msg_bits, 4)
+    rng = np.random.default_rng(4242 + rank)
+    msgs = rng.integers(0, 1 << bits, S).astype(np.uint64)
+    table = (np.arange(1 << bits) ** 2 % (1 << bits)).astype(np.uint64)
+    d_lut = eng.to_device(trivial_glwe(expand_lut(table, p.N, bits), p.k))
+    d_cts = eng.to_device(ks.encrypt_big(msgs, bits, seed=2000 + rank))
+    d_idx = torch.zeros(S, dtype=torch.int64, device=eng.device)
+    d_out = torch.empty((S, p.big_n + 1), dtype=torch.int64, device=eng.device)
+    d_mid = torch.empty((S, p.n + 1), dtype=torch.int64, device=eng.device)
+    iota = eng.iota(S)
+
+    def step():
+        eng.keyswitch_bootstrap(d_cts, d_ksk, d_fbsk, d_lut, d_idx, p, out=d_out, ks_tmp=d_mid)
+
+    ms = _events_ms(step, 3, steps)
+    pbs_ms = _events_ms(lambda: eng.bootstrap(d_mid, d_lut, d_idx, d_fbsk, p.n, p.k, p.N, p.b, p.l,
+                                              out=d_out, in_idx=iota, out_idx=iota), 1, steps)
+    nchk = min(S, 256)
+    ok = bool(np.array_equal(ks.decrypt_big(as_u64(d_out[:nchk]), bits), table[msgs[:nchk]]))
+    return {"config": label, "params": name, "samples_per_gpu": S, "value": S / (ms * 1e-3),
+            "unit": UNIT, "ms_per_step": ms, "us_per_pbs": ms * 1e3 / S, "steps": steps, "warmup": 3,
+            "roofline": _frac(p, S, pbs_ms, fp64_peak), "verified_decryptions": ok}
+
+
+def leg_cfg4(eng, kc, total_tlus, world, rank, steps, fp64_peak):
+    """configs[3]: a dense layer (clear +-1 weights x encrypted activations, leveled ops on the
+    device) followed by ReLU table lookups on the whole layer, P8 (N = 16384, l = 2).  The layer
+    is 64 neurons wide; `total_tlus`/64 input vectors of 64 encrypted features are sharded over
+    the ranks by input vector (strong scaling: the layer is fixed, every rank owns a contiguous
+    slice of the batch)."""
+    import torch
+    from concrete_b200 import as_u64
+    from concrete_b200.sharding import shard_range
+    from harness import expand_lut, trivial_glwe
+
+    ks, d_ksk, d_fbsk = kc.get("P8")
+    p = ks.p
+    bits, feats, neurons, taps = 7, 64, 64, 8
+    _, vecs = shard_range(total_tlus // neurons, world, rank)
+    S = vecs * neurons
+    rng = np.random.default_rng(64)                       # the layer (same on every rank)
+    sel = np.stack([rng.choice(feats, taps, replace=False) for _ in range(neurons)])
+    sgn = rng.choice([-1, 1], size=(neurons, taps)).astype(np.int64)
+    bias = rng.integers(-6, 7, size=neurons).astype(np.int64)
+    rng = np.random.default_rng(640 + rank)               # this rank's activations
+    x = rng.integers(0, 8, size=(vecs, feats)).astype(np.int64)
+    z = (x[:, sel] * sgn[None]).sum(axis=2) + bias[None]
+    half = 1 << (bits - 1)
+    assert np.abs(z).max() < half
+    table = np.array([max(v - half, 0) for v in range(1 << bits)], dtype=np.uint64)
+    d_lut = eng.to_device(trivial_glwe(expand_lut(table, p.N, bits), p.k))
+    d_x = eng.to_device(ks.encrypt_big(x.reshape(-1).astype(np.uint64), bits, seed=3000 + rank))
+    base = (np.arange(vecs) * feats)[:, None]
+    d_gather = [torch.from_numpy((base + sel[None, :, t]).reshape(-1)).to(eng.device)
+                for t in range(taps)]
+    d_w = [eng.to_device(np.tile(sgn[:, t].astype(np.uint64), vecs)) for t in range(taps)]
+    d_b = eng.to_device(np.tile(((bias + half).astype(np.uint64) << np.uint64(63 - bits)), vecs))
+    add, mul_clear, add_plain = _dev_ops(eng)
+    d_idx = torch.zeros(S, dtype=torch.int64, device=eng.device)
+    d_out = torch.empty((S, p.big_n + 1), dtype=torch.int64, device=eng.device)
+    d_mid = torch.empty((S, p.n + 1), dtype=torch.int64, device=eng.device)
+    d_acc = torch.empty((S, p.big_n + 1), dtype=torch.int64, device=eng.device)
+    d_tmp = torch.empty_like(d_acc)
+    d_row = torch.empty_like(d_acc)
+    iota = eng.iota(S)
+
+    def step():
+        for t in range(taps):                             # z_j = sum_t w_jt * x_sel(j,t) + b_j
+            torch.index_select(d_x, 0, d_gather[t], out=d_row)   # row gather: plumbing
+            if t == 0:
+                mul_clear(d_row, d_w[t], p.big_n, out=d_acc)
+            else:
+                mul_clear(d_row, d_w[t], p.big_n, out=d_tmp)
+                add(d_acc, d_tmp, p.big_n, out=d_acc)
+        add_plain(d_acc, d_b, p.big_n, out=d_acc)
+        eng.keyswitch_bootstrap(d_acc, d_ksk, d_fbsk, d_lut, d_idx, p, out=d_out, ks_tmp=d_mid)
+
+    ms = _events_ms(step, 3, steps)
+    pbs_ms = _events_ms(lambda: eng.bootstrap(d_mid, d_lut, d_idx, d_fbsk, p.n, p.k, p.N, p.b, p.l,
+                                              out=d_out, in_idx=iota, out_idx=iota), 1, steps)
+    nchk = min(S, 256)
+    got = ks.decrypt_big(as_u64(d_out[:nchk]), bits)
+    ok = bool(np.array_equal(got, np.maximum(z, 0).reshape(-1)[:nchk].astype(np.uint64)))
+    return ms, {"config": "configs[3]: dense layer (leveled, device) + ReLU TLUs, P8",
+                "params": "P8", "layer": f"{neurons} neurons x {taps} taps of +-1, {feats} features",
+                "tlus_total": total_tlus, "tlus_this_gpu": S, "scaling": "strong",
+                "unit": "TLU/s", "steps": steps, "warmup": 3,
+                "roofline": _frac(p, S, pbs_ms, fp64_peak), "verified_decryptions": ok}
+
+
+def leg_cfg5(eng, kc, ops, steps, fp64_peak):
+    """configs[4]: 16-bit additions on values held as 8 chunks of 2 bits in 4-bit ciphertexts (P4):
+    per addition 8 strictly dependent carry rounds (leveled add, keyswitch, PBS; BigInt.cpp:109-154)
+    and one per-chunk TLU round; `ops` independent additions in flight, so every dependent round
+    is a batch of `ops` and the last one a batch of 8 * ops."""
+    import torch
+    from concrete_b200 import as_u64
+    from harness import expand_lut, trivial_glwe
+
+    ks, d_ksk, d_fbsk = kc.get("P4")
+    p = ks.p
+    bits, chunks = 4, 8
+    rng = np.random.default_rng(16)
+    a = rng.integers(0, 1 << 16, ops)
+    b = rng.integers(0, 1 << 16, ops)
+    # chunk-major layout [chunk][op] so that every round reads one contiguous slice
+    split = lambda v: np.stack([(v >> (2 * c)) & 3 for c in range(chunks)], axis=0).astype(np.uint64)
+    d_a = eng.to_device(ks.encrypt_big(split(a).reshape(-1), bits, seed=21))
+    d_b = eng.to_device(ks.encrypt_big(split(b).reshape(-1), bits, seed=22))
+    d_lut_carry = eng.to_device(trivial_glwe(expand_lut((np.arange(16) >> 2).astype(np.uint64), p.N, bits), p.k))
+    d_lut_low = eng.to_device(trivial_glwe(expand_lut((np.arange(16) & 3).astype(np.uint64), p.N, bits), p.k))
+    add, _, _ = _dev_ops(eng)
+    W = p.big_n + 1
+    d_sum = torch.empty((chunks * ops, W), dtype=torch.int64, device=eng.device)
+    d_carry = torch.empty((ops, W), dtype=torch.int64, device=eng.device)
+    d_low = torch.empty((chunks * ops, W), dtype=torch.int64, device=eng.device)
+    d_mid = torch.empty((chunks * ops, p.n + 1), dtype=torch.int64, device=eng.device)
+    d_idx = torch.zeros(chunks * ops, dtype=torch.int64, device=eng.device)
+
+    def step():
+        add(d_a, d_b, p.big_n, out=d_sum)
+        for c in range(chunks):                           # 8 dependent KS+PBS rounds
+            s_c = d_sum[c * ops:(c + 1) * ops]
+            if c:
+                add(s_c, d_carry, p.big_n, out=s_c)
+            eng.keyswitch_bootstrap(s_c, d_ksk, d_fbsk, d_lut_carry, d_idx, p, out=d_carry,
+                                    ks_tmp=d_mid)
+        eng.keyswitch_bootstrap(d_sum, d_ksk, d_fbsk, d_lut_low, d_idx, p, out=d_low, ks_tmp=d_mid)
+
+    ms = _events_ms(step, 3, steps)
+    nchk = min(ops, 128)
+    low = ks.decrypt_big(as_u64(d_low).reshape(chunks, ops, W)[:, :nchk].reshape(-1, W), bits)
+    low = low.reshape(chunks, nchk).astype(np.int64)
+    total = sum(low[c] << (2 * c) for c in range(chunks))
+    carry = ks.decrypt_big(as_u64(d_carry[:nchk]), bits).astype(np.int64)
+    ok = bool(np.array_equal(total, (a[:nchk] + b[:nchk]) & 0xFFFF)
+              and np.array_equal(carry, (a[:nchk] + b[:nchk]) >> 16))
+    pbs = 2 * chunks * ops
+    return {"config": "configs[4]: chunked 16-bit add (8 dependent KS+PBS rounds + 1 TLU round), P4",
+            "params": "P4", "ops_in_flight": ops, "value": ops / (ms * 1e-3), "unit": "16-bit add/s",
+            "pbs_per_s": pbs / (ms * 1e-3), "pbs_per_add": 2 * chunks, "ms_per_step": ms,
+            "steps": steps, "warmup": 3, "verified_sums": ok,
+            "roofline": {"bound": "fp64", "unit": "TFLOP/s", "peak": fp64_peak,
+                         "achieved": pbs * p.pbs_flops() / (ms * 1e-3) / 1e12,
+                         "frac": pbs * p.pbs_flops() / (ms * 1e-3) / 1e12 / fp64_peak,
+                         "note": "whole step (leveled adds + keyswitches included in the time)"}}
 
 
 def run_ours(args):
@@ -414,6 +646,76 @@ def run_ours(args):
         except Exception as e:  # the witness is optional infrastructure
             ref_gpu_line = {"unavailable": repr(e)[:200]}
 
+    # ---- the other BASELINE.json configs, short timed legs (each: 3 warm-ups + config_steps) ------
+    configs = None
+    default_run = (args.workload == "P2048" and S == 16384 and not args.pbs_plan)
+    if default_run and not args.no_configs:
+        kc = KeyCache(eng)
+        cs = args.config_steps
+        configs = {"configs[1]": "this line (P2048 x 16384 per GPU)"}
+        if world == 1:
+            configs["configs[0]"] = leg_ks_pbs(eng, kc, "P4", 64, 10 * cs, fp64_peak, rank,
+                                               "configs[0]: 4-bit TLU on 64 encrypted uint4, P4")
+            configs["configs[4]"] = leg_cfg5(eng, kc, 4096, cs, fp64_peak)
+            kc.drop("P4")
+            configs["configs[2] N=8192"] = leg_ks_pbs(eng, kc, "P7", 4096, cs, fp64_peak, rank,
+                                                      "configs[2]: P7 (N=8192) x 4096")
+            kc.drop("P7")
+            torch.cuda.empty_cache()
+            configs["configs[2] N=16384"] = leg_ks_pbs(eng, kc, "P8", 4096, cs, fp64_peak, rank,
+                                                       "configs[2]: P8 (N=16384, l=2) x 4096")
+        barrier()
+        ms4, c4 = leg_cfg4(eng, kc, 4096, world, rank, cs, fp64_peak)
+        barrier()
+        ms4 = max_over_ranks(ms4)
+        c4.update({"value": 4096 / (ms4 * 1e-3), "ms_per_step": ms4, "n_gpus": world})
+        configs["configs[3]"] = c4
+        kc.drop("P8")
+        torch.cuda.empty_cache()
+
+    # ---- in-library multi-GPU: ONE process shards a host batch over all GPUs of the box through the
+    # runtime wrappers (csrc/wrappers.cpp for_each_shard: one host thread + stream per device, the
+    # GPUDFG.cpp:852-895 analogue).  Rank 0 drives it while the other ranks wait on a HOST barrier.
+    inlib = None
+    if default_run and world > 1 and not args.no_inlib:
+        hb = dist.new_group(backend="gloo")
+        dist.barrier(group=hb)
+        if rank == 0:
+            try:
+                tot = world * S
+                rt = Runtime(num_gpus=world, device_base=0)
+                ki, bi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk)
+                reps = -(-tot // len(cts_host))
+                h_in = torch.from_numpy(np.tile(cts_host, (reps, 1))[:tot].view(np.int64)) \
+                    .pin_memory().numpy().view(np.uint64)
+                h_mid = torch.empty((tot, p.n + 1), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+                h_out = torch.empty((tot, p.big_n + 1), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+
+                def inlib_step():
+                    rt.batched_keyswitch(h_mid, h_in, p.l_ks, p.b_ks, p.big_n, p.n, ki)
+                    rt.batched_bootstrap(h_out, h_mid, lut_poly, p.n, p.N, p.l, p.b, p.k, bi)
+
+                for _ in range(2):
+                    inlib_step()
+                t0 = time.perf_counter()
+                for _ in range(args.steps):
+                    inlib_step()
+                il_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+                pick = np.arange(0, tot, max(1, tot // 512))[:512]
+                ok3 = bool(np.array_equal(ks.decrypt_big(np.ascontiguousarray(h_out[pick]), bits),
+                                          table[np.tile(msgs, reps)[:tot][pick]]))
+                inlib = {"value": tot / (il_ms * 1e-3), "unit": UNIT, "ms_per_step": il_ms,
+                         "n_gpus": world, "global_batch": tot,
+                         "api": "ONE process: memref_batched_keyswitch_lwe_cuda_u64 + "
+                                "memref_batched_bootstrap_lwe_cuda_u64 with Runtime(num_gpus=N) "
+                                "(host buffers, H2D/D2H inside, host clock)",
+                         "verified_decryptions": ok3}
+                rt.close()
+                del h_in, h_mid, h_out
+            except Exception as e:
+                inlib = {"unavailable": repr(e)[:300]}
+        dist.barrier(group=hb)
+
     # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -431,6 +733,9 @@ def run_ours(args):
             "us_per_pbs": ms_step * 1e3 / S, "step_ms_rank0": step_ms, "gpu_launches": launches,
             "verified_decryptions": verified, "clocks": clocks, "roofline": roofline,
             "e2e": e2e, "cpu_baseline": cpu, "reference_gpu": ref_gpu_line,
+            "vs_reference_gpu": (value / ref_gpu_line["value"]
+                                 if ref_gpu_line and ref_gpu_line.get("value") else None),
+            "configs": configs, "in_library_multi_gpu": inlib,
         }
         print(json.dumps(line), flush=True)
     eng.close()

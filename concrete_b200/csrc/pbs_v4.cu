@@ -13,12 +13,13 @@ struct V4Variant {
   void (*multi_wide)(const PbsArgs);   // l >= 2, base_log * l  > 31
   void (*convert)(double2 *, const double2 *, size_t);
   int threads, T, cpb, logm;
+  int cluster; // CTAs per ciphertext (k+1 in the cluster variant, else 1)
   size_t smem, smem_stash, convert_smem;
 };
 
-template <int K, int LOGN, int CPB, int RB, int NB> V4Variant make_v4() {
-  using C1 = v4::Cfg<K, LOGN, 4, CPB, false, RB, NB>;
-  using CL = v4::Cfg<K, LOGN, 4, CPB, true, RB, NB>;
+template <int K, int LOGN, int CPB, int RB, int NB, bool CLUSTER = false> V4Variant make_v4() {
+  using C1 = v4::Cfg<K, LOGN, 4, CPB, false, RB, NB, CLUSTER>;
+  using CL = v4::Cfg<K, LOGN, 4, CPB, true, RB, NB, CLUSTER>;
   V4Variant v;
   v.one_level = v4::pbs_kernel_v4<C1, true, 1>;
   v.multi_narrow = v4::pbs_kernel_v4<CL, true, 0>;
@@ -27,6 +28,7 @@ template <int K, int LOGN, int CPB, int RB, int NB> V4Variant make_v4() {
   v.threads = C1::THREADS;
   v.T = C1::T;
   v.cpb = CPB;
+  v.cluster = CLUSTER ? K + 1 : 1;
   v.logm = C1::LOGM;
   v.smem = C1::SMEM;
   v.smem_stash = CL::SMEM;
@@ -34,9 +36,9 @@ template <int K, int LOGN, int CPB, int RB, int NB> V4Variant make_v4() {
   return v;
 }
 
-// shapes: every k = 1 polynomial size of the BASELINE configs from 1024 up to 8192, and P4's
-// (k = 2, N = 1024).  N = 16384 needs the two polynomials of a ciphertext on two SMs (256 KiB of
-// accumulator): see pbs_v4 cluster notes in DESIGN.md.
+// shapes: every k = 1 polynomial size of the BASELINE configs from 1024 up to 16384, and P4's
+// (k = 2, N = 1024).  At N = 16384 one polynomial buffer is 128 KiB: the two polynomials of a
+// ciphertext live on the two SMs of a thread-block cluster (Cfg::CL).
 bool v4_variant(u32 k, u32 N, V4Variant &v) {
   // <k, log2 N, ciphertexts per CTA, rows per ring block, ring blocks>: RB * NB of the 16 rows of a
   // GGSW level are resident; the whole level where the shared memory left by the buffers allows
@@ -44,6 +46,7 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   if (k == 1 && N == 2048) { v = make_v4<1, 11, 4, 8, 2>(); return true; }  // 128 + 64 KiB
   if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
+  if (k == 1 && N == 16384) { v = make_v4<1, 14, 1, 2, 3, true>(); return true; } // 128 + 96 KiB
   if (k == 2 && N == 1024) { v = make_v4<2, 10, 5, 8, 2>(); return true; }  // 120 + 72 KiB
   return false;
 }
@@ -51,7 +54,8 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
 } // namespace
 
 bool cb_pbs_v4_shape(u32 k, u32 N) {
-  return (k == 1 && (N == 1024 || N == 2048 || N == 4096 || N == 8192)) || (k == 2 && N == 1024);
+  return (k == 1 && (N == 1024 || N == 2048 || N == 4096 || N == 8192 || N == 16384)) ||
+         (k == 2 && N == 1024);
 }
 
 int cb_pbs_v4_cpb(u32 k, u32 N) {
@@ -102,8 +106,45 @@ void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out
   CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int sms = 0;
   CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
-  const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
-  kern<<<grid, v.threads, smem, stream>>>(a);
-  CB_CHECK(cudaGetLastError());
+  if (v.cluster == 1) {
+    const u32 grid = std::min<u32>((u32)sms, num_samples); // the kernel balances the tail
+    kern<<<grid, v.threads, smem, stream>>>(a);
+    CB_CHECK(cudaGetLastError());
+    CB_LAUNCHED();
+    return;
+  }
+  // cluster variant: one cluster of k+1 CTAs per ciphertext, as many clusters as are co-resident
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3((u32)v.threads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr;
+  attr.id = cudaLaunchAttributeClusterDimension;
+  attr.val.clusterDim.x = (u32)v.cluster;
+  attr.val.clusterDim.y = 1;
+  attr.val.clusterDim.z = 1;
+  cfg.attrs = &attr;
+  cfg.numAttrs = 1;
+  int clusters = 0;
+  {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void *>, int> cache; // (device, kernel) -> clusters
+    std::lock_guard<std::mutex> g(mu);
+    auto key = std::make_pair(gpu, (const void *)kern);
+    auto it = cache.find(key);
+    if (it == cache.end()) {
+      cfg.gridDim = dim3((u32)(sms / v.cluster) * v.cluster, 1, 1);
+      int c = 0;
+      if (cudaOccupancyMaxActiveClusters(&c, kern, &cfg) != cudaSuccess || c < 1) {
+        (void)cudaGetLastError();
+        c = sms / v.cluster / 2; // conservative
+      }
+      it = cache.emplace(key, c).first;
+    }
+    clusters = it->second;
+  }
+  clusters = (int)std::min<u32>((u32)clusters, num_samples);
+  cfg.gridDim = dim3((u32)clusters * v.cluster, 1, 1);
+  CB_CHECK(cudaLaunchKernelEx(&cfg, kern, a));
   CB_LAUNCHED();
 }

@@ -27,10 +27,18 @@
 namespace v4 {
 using namespace sm100;
 
-template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int NB_ = 2> struct Cfg {
+template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int NB_ = 2,
+          bool CL_ = false>
+struct Cfg {
   static constexpr int K = K_, LOGN = LOGN_, LOGM = LOGN_ - 1, M = 1 << LOGM, N = 2 * M;
   static constexpr int LOGP = LOGP_, P = 1 << LOGP_, T = M / P;
-  static constexpr int GS = K_ + 1, CPB = CPB_, GROUPS = CPB_ * GS, THREADS = GROUPS * T;
+  // CL: the k+1 groups of ONE ciphertext are the k+1 CTAs of a thread-block cluster (one
+  // polynomial per SM: N = 16384, where one polynomial buffer is 128 KiB).  A CTA then holds one
+  // group, consumes only column r of every GGSW level (r = its rank in the cluster) and reads the
+  // partners' parked transforms through distributed shared memory.
+  static constexpr bool CL = CL_;
+  static constexpr int GS = K_ + 1, CPB = CPB_, GROUPS = CL_ ? 1 : CPB_ * GS, THREADS = GROUPS * T;
+  static constexpr int KEY_POLYS = CL_ ? GS : GS * GS; // key polynomials of a level a CTA consumes
   static constexpr int NWARPS = THREADS / 32;
   static constexpr bool STASH = STASH_; // l >= 2: Fourier accumulators parked in TMEM
   static constexpr u32 BUF_BYTES = (u32)M * 16;
@@ -42,7 +50,7 @@ template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int 
   // what the shared memory left by the buffers holds: the whole level when it fits.
   static constexpr int RB = RB_, NB = NB_, BLOCKS_PER_LEVEL = P / RB_;
   static constexpr u32 POLY_BLOCK_BYTES = (u32)RB_ * ROW_BYTES;         // RB rows of one polynomial
-  static constexpr u32 BLOCK_BYTES = (u32)GS * GS * POLY_BLOCK_BYTES;   // RB rows of one level
+  static constexpr u32 BLOCK_BYTES = (u32)KEY_POLYS * POLY_BLOCK_BYTES; // RB rows of one level
   static constexpr u32 OFF_RING = (u32)GROUPS * BUF_BYTES;
   static constexpr u32 OFF_CTRL = OFF_RING + NB_ * BLOCK_BYTES;
   static constexpr size_t SMEM = (size_t)OFF_CTRL + 256;
@@ -55,6 +63,7 @@ template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int 
   static_assert(P % RB_ == 0 && NB_ >= 1 && NB_ <= 16, "ring shape");
   static_assert(SMEM <= 232448, "shared memory");
   static_assert(T == 32 || CPB_ + GROUPS <= 15, "named barriers");
+  static_assert(!CL_ || CPB_ == 1, "cluster variant: one ciphertext per cluster");
 };
 
 struct Ctrl {
@@ -88,8 +97,30 @@ template <class C> __device__ __forceinline__ void grp_bar(int grp) {
     asm volatile("bar.sync %0, %1;" ::"r"(1 + C::CPB + grp), "n"(C::T) : "memory");
   }
 }
+__device__ __forceinline__ u32 cluster_rank() {
+  u32 r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// every group of ciphertext `ct`: a named barrier inside the CTA, or the cluster barrier
 template <class C> __device__ __forceinline__ void ct_bar(int ct) {
-  asm volatile("bar.sync %0, %1;" ::"r"(1 + ct), "n"(C::GS * C::T) : "memory");
+  if constexpr (C::CL) {
+    cluster_arrive();
+    cluster_wait();
+  } else {
+    asm volatile("bar.sync %0, %1;" ::"r"(1 + ct), "n"(C::GS * C::T) : "memory");
+  }
+}
+// (group index inside the CTA, polynomial index r of the group, ciphertext slot of the CTA)
+template <class C> __device__ __forceinline__ int poly_of(int grp) {
+  if constexpr (C::CL) return (int)cluster_rank();
+  else return grp % C::GS;
 }
 
 // ---- transforms: the passes of fft.cuh with an XOR-swizzled exchange ---------------------------
@@ -150,8 +181,12 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, in
 
 // In: x[r] = z_{t + r*T}.  Out: x[r] = F_{q = t*P + r}.  Every exchange is barrier / write /
 // barrier / read, so the buffer may have other readers right up to the call.
+// `pending` (cluster variant): the partners may still be reading this CTA's buffer (their product
+// phase); the cluster barrier they arrive at afterwards is waited for right before the first
+// exchange write, i.e. behind the register-only stages of the first pass.
 template <class C>
-__device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__restrict__ tw) {
+__device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__restrict__ tw,
+                                        bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
 #pragma unroll
   for (int pass = 0; pass < C::NPASS; ++pass) {
@@ -163,6 +198,9 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
     fwd_stages<C>(x, t, lo, s0, s1, tw);
     if (pass + 1 < C::NPASS) {
       const int lo2 = pass_lo<C>(pass + 1);
+      if constexpr (C::CL) {
+        if (pass == 0 && pending) cluster_wait();
+      }
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
@@ -175,7 +213,8 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
 
 // In: x[r] = F_{t*P + r}.  Out: x[r] = M * z_{t + r*T} (unnormalised).
 template <class C>
-__device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__restrict__ tw) {
+__device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__restrict__ tw,
+                                        bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
 #pragma unroll
   for (int pass = C::NPASS - 1; pass >= 0; --pass) {
@@ -187,6 +226,9 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
     inv_stages<C>(x, t, lo, s1, s0, tw);
     if (pass > 0) {
       const int lo2 = pass_lo<C>(pass - 1);
+      if constexpr (C::CL) {
+        if (pass == C::NPASS - 1 && pending) cluster_wait();
+      }
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
@@ -208,21 +250,24 @@ template <class C> __device__ __noinline__ void issue_block(u32 i, u32 m, u32 b,
   const u32 level = ctrl->level;
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
   mbar_expect_tx(&ctrl->full_bar[slot], C::BLOCK_BYTES);
-  const double2 *src =
-      bsk + ((size_t)i * level + m) * C::GS * C::GS * C::M + (size_t)b * C::RB * C::T;
+  // cluster variant: this CTA consumes column r only: key polynomials (rr, r), rr = 0..k
+  const size_t col = C::CL ? (size_t)cluster_rank() : 0, pstride = C::CL ? C::GS : 1;
+  const double2 *src = bsk + (((size_t)i * level + m) * C::GS * C::GS + col) * C::M +
+                       (size_t)b * C::RB * C::T;
   unsigned char *dst = smem + C::OFF_RING + slot * C::BLOCK_BYTES;
 #pragma unroll
-  for (int poly = 0; poly < C::GS * C::GS; ++poly)
-    tma_load_bulk(dst + poly * C::POLY_BLOCK_BYTES, src + (size_t)poly * C::M, C::POLY_BLOCK_BYTES,
-                  &ctrl->full_bar[slot]);
+  for (int poly = 0; poly < C::KEY_POLYS; ++poly)
+    tma_load_bulk(dst + poly * C::POLY_BLOCK_BYTES, src + (size_t)poly * pstride * C::M,
+                  C::POLY_BLOCK_BYTES, &ctrl->full_bar[slot]);
   // Keys that do not fit the 126 MB L2 (N >= 4096: 115 MB .. 240 MB): all CTAs walk the GGSW index
   // together, so ONE early request per block turns every later fill into an L2 hit.  An eighth of
   // the CTAs asks for the same block two GGSWs ahead.
   if (C::LOGN >= 12 && (blockIdx.x & 7u) == (b & 7u) && i + 2 < ctrl->n) {
     const double2 *ahead = src + (size_t)2 * level * C::GS * C::GS * C::M;
 #pragma unroll
-    for (int poly = 0; poly < C::GS * C::GS; ++poly)
-      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ahead + (size_t)poly * C::M),
+    for (int poly = 0; poly < C::KEY_POLYS; ++poly)
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ahead +
+                                                                       (size_t)poly * pstride * C::M),
                    "n"(C::POLY_BLOCK_BYTES)
                    : "memory");
   }
@@ -368,7 +413,9 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
         x[p].y = __int2double_rn((int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
       }
     }
-    forward<C>(x, tw); // its first barrier also ends the rotated reads of ACC
+    // its first barrier also ends the rotated reads of ACC; for m > 0 of the cluster variant the
+    // partners' reads of the previous level's parked transform end at the pending cluster barrier
+    forward<C>(x, tw, C::CL && m > 0);
     {
       const int tid = opaque_tid(), t = tid % T, grp = tid / T;
       double2 *buf = reinterpret_cast<double2 *>(smem + (size_t)grp * C::BUF_BYTES);
@@ -381,17 +428,56 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
     // ---- phase B: column r of the external product, in place in x
     {
       const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5, lane = tid & 31;
-      const int ct = grp / GS, r = grp % GS;
+      const int ct = C::CL ? 0 : grp / GS, r = poly_of<C>(grp);
       const u32 tm_stash = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
                            (u32)(warp >> 2) * C::TM_PER_WARP + C::TM_OWN;
-      const u32 ring = smem_u32(smem) + C::OFF_RING + (u32)t * 16 + (u32)r * C::POLY_BLOCK_BYTES;
+      // key polynomial (rr, r) of the block: at rr * GS + r (whole level staged) or at rr (cluster
+      // variant: only column r is staged)
+      const u32 ring = smem_u32(smem) + C::OFF_RING + (u32)t * 16 +
+                       (C::CL ? 0u : (u32)r * C::POLY_BLOCK_BYTES);
+      constexpr u32 KEY_RR_STRIDE = (u32)GS * C::POLY_BLOCK_BYTES;
       const u32 sib = smem_u32(smem) + (u32)(ct * GS) * C::BUF_BYTES + (u32)t * 16;
+      // cluster variant: the partners' buffers through distributed shared memory, fetched one
+      // ring block ahead of their use (a remote load takes ~200 cycles)
+      // (partner j of this CTA is the CTA of rank (r + 1 + j) mod (k+1))
+      constexpr int NSIB = C::CL ? GS - 1 : 1;
+      u32 sib_cl[NSIB], key_cl[NSIB];
+      double2 fs[NSIB][C::RB];
+      if constexpr (C::CL) {
+#pragma unroll
+        for (int j = 0; j < NSIB; ++j) {
+          const u32 rr = (u32)(r + 1 + j) % (u32)GS;
+          key_cl[j] = rr * C::POLY_BLOCK_BYTES;
+          asm volatile("mapa.shared::cluster.u32 %0, %1, %2;"
+                       : "=r"(sib_cl[j])
+                       : "r"(smem_u32(smem) + (u32)t * 16), "r"(rr));
+        }
+#pragma unroll
+        for (int j = 0; j < NSIB; ++j)
+#pragma unroll
+          for (int pr = 0; pr < C::RB; ++pr)
+            asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];"
+                         : "=d"(fs[j][pr].x), "=d"(fs[j][pr].y)
+                         : "r"(sib_cl[j] + (u32)(pr * T * 16)));
+      }
       u32 blk = blk0 + m * C::BLOCKS_PER_LEVEL;
       RingPos rp = ring_pos<C>(blk);
 #pragma unroll
       for (int b = 0; b < C::BLOCKS_PER_LEVEL; ++b, ++blk) {
         wait_block<C>(rp);
         const u32 slot = ring + rp.slot * C::BLOCK_BYTES;
+        double2 fn[NSIB][C::RB];
+        if constexpr (C::CL) {
+          if (b + 1 < C::BLOCKS_PER_LEVEL) {
+#pragma unroll
+            for (int j = 0; j < NSIB; ++j)
+#pragma unroll
+              for (int pr = 0; pr < C::RB; ++pr)
+                asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];"
+                             : "=d"(fn[j][pr].x), "=d"(fn[j][pr].y)
+                             : "r"(sib_cl[j] + (u32)(((b + 1) * C::RB + pr) * T * 16)));
+          }
+        }
 #pragma unroll
         for (int pr = 0; pr < C::RB; ++pr) {
           const int p = b * C::RB + pr;
@@ -406,28 +492,55 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
             o = make_double2(__hiloint2double((int)v[1], (int)v[0]),
                              __hiloint2double((int)v[3], (int)v[2]));
           }
-#pragma unroll
-          for (int rr = 0; rr < GS; ++rr) {
-            double2 w, f;
+          if constexpr (C::CL) { // own term, then the partners' (order of the sum is free)
+            double2 w;
             asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
                          : "=d"(w.x), "=d"(w.y)
-                         : "r"(slot + (u32)(rr * GS) * C::POLY_BLOCK_BYTES + (u32)pr * C::ROW_BYTES));
-            if (rr == r) {
-              f = x[p];
-            } else {
+                         : "r"(slot + (u32)r * C::POLY_BLOCK_BYTES + (u32)pr * C::ROW_BYTES));
+            o.x = fma(x[p].x, w.x, fma(-x[p].y, w.y, o.x));
+            o.y = fma(x[p].x, w.y, fma(x[p].y, w.x, o.y));
+#pragma unroll
+            for (int j = 0; j < NSIB; ++j) {
               asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
-                           : "=d"(f.x), "=d"(f.y)
-                           : "r"(sib + (u32)rr * C::BUF_BYTES + (u32)(p * T * 16)));
+                           : "=d"(w.x), "=d"(w.y)
+                           : "r"(slot + key_cl[j] + (u32)pr * C::ROW_BYTES));
+              const double2 f = fs[j][pr];
+              o.x = fma(f.x, w.x, fma(-f.y, w.y, o.x));
+              o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
             }
-            o.x = fma(f.x, w.x, fma(-f.y, w.y, o.x));
-            o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
+          } else {
+#pragma unroll
+            for (int rr = 0; rr < GS; ++rr) {
+              double2 w, f;
+              asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                           : "=d"(w.x), "=d"(w.y)
+                           : "r"(slot + (u32)rr * KEY_RR_STRIDE + (u32)pr * C::ROW_BYTES));
+              if (rr == r) {
+                f = x[p];
+              } else {
+                asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                             : "=d"(f.x), "=d"(f.y)
+                             : "r"(sib + (u32)rr * C::BUF_BYTES + (u32)(p * T * 16)));
+              }
+              o.x = fma(f.x, w.x, fma(-f.y, w.y, o.x));
+              o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
+            }
           }
           x[p] = o;
+        }
+        if constexpr (C::CL) {
+#pragma unroll
+          for (int j = 0; j < NSIB; ++j)
+#pragma unroll
+            for (int pr = 0; pr < C::RB; ++pr) fs[j][pr] = fn[j][pr];
         }
         block_done<C>(lane, i, m, (u32)b, blk, rp.slot);
         ring_next<C>(rp);
       }
-      ct_bar<C>(ct); // every read of the parked transforms done before the buffers are reused
+      // every read of the parked transforms done before the buffers are reused; the cluster
+      // variant only ARRIVES here and waits behind the register stages of the next transform
+      if constexpr (C::CL) cluster_arrive();
+      else ct_bar<C>(ct);
       if (C::STASH && m + 1 < level) {
 #pragma unroll
         for (int c4 = 0; c4 < P / 4; ++c4) {
@@ -447,7 +560,7 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
   }
 
   // ---- phase C: inverse transform, torus rounding, ACC += (own copy in TMEM, home in smem)
-  inverse<C>(x, tw);
+  inverse<C>(x, tw, C::CL);
   {
     const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5;
     ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
@@ -481,20 +594,23 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
   constexpr int P = C::P, T = C::T, M = C::M, N = C::N, GS = C::GS, K = C::K, CPB = C::CPB;
   extern __shared__ __align__(1024) unsigned char smem[];
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int grp = tid / T, t = tid % T, ct = grp / GS, r = grp % GS;
+  const int grp = tid / T, t = tid % T, ct = C::CL ? 0 : grp / GS, r = poly_of<C>(grp);
   ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
   Ctrl *ctrl = reinterpret_cast<Ctrl *>(smem + C::OFF_CTRL);
   const u32 n = a.n, level = LV ? (u32)LV : a.level;
   const size_t out_size = (size_t)K * N + 1;
+  // scheduling unit: a CTA, or a cluster of k+1 CTAs working on one ciphertext
+  const u32 num_units = C::CL ? gridDim.x / GS : gridDim.x;
+  const u32 unit = C::CL ? blockIdx.x / GS : blockIdx.x;
 
   // Sample -> (CTA, round, slot), as in pbs_kernel_w32v3: `full` rounds with CPB ciphertexts in
   // every CTA, then the remainder spread evenly over all CTAs in one last (shorter) round.
-  const u32 wave = gridDim.x * CPB;
+  const u32 wave = num_units * CPB;
   const u32 full = a.num_samples / wave;
   const u32 rem = a.num_samples - full * wave;
-  const u32 rem_base = rem / gridDim.x, rem_extra = rem % gridDim.x;
-  const u32 my_rem = rem_base + (blockIdx.x < rem_extra ? 1u : 0u);
-  const u32 rem_first = full * wave + blockIdx.x * rem_base + min(blockIdx.x, rem_extra);
+  const u32 rem_base = rem / num_units, rem_extra = rem % num_units;
+  const u32 my_rem = rem_base + (unit < rem_extra ? 1u : 0u);
+  const u32 rem_first = full * wave + unit * rem_base + min(unit, rem_extra);
   const u32 rounds = full + (my_rem ? 1u : 0u);
   const u32 blocks_per_cmux = level * C::BLOCKS_PER_LEVEL;
   const u32 total_blocks = rounds * n * blocks_per_cmux;
@@ -535,7 +651,7 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
   u32 blk0 = 0; // block number of (current CMUX, level 0, block 0)
   for (u32 rd = 0; rd < rounds; ++rd) {
     const bool active = rd < full || (u32)ct < my_rem;
-    const u32 sample = rd < full ? rd * wave + blockIdx.x * CPB + ct : rem_first + ct;
+    const u32 sample = rd < full ? rd * wave + unit * CPB + ct : rem_first + ct;
     const u64 *lwe = a.lwe_in + (active ? a.in_idx[sample] : 0) * (u64)(n + 1);
 
     if (active) { // ACC_r <- LUT_r * X^(-b_hat)   (polynomial_algorithms.rs:500-539)
@@ -600,6 +716,10 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
     grp_bar<C>(grp);
   }
 
+  if constexpr (C::CL) { // no CTA leaves while a partner may still read its shared memory
+    cluster_arrive();
+    cluster_wait();
+  }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   if (warp == 0)

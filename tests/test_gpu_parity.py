@@ -272,7 +272,7 @@ def test_pbs_reference_parameter_table(engine, k, N, b, l, sig_glwe):
     _pbs_check(engine, KeySet(prm, seed=42), 9, 2, use_ks=False)
 
 
-@pytest.mark.parametrize("name,n_small", [("TOY512", None), ("P4", 24), ("P7", 16)])
+@pytest.mark.parametrize("name,n_small", [("TOY512", None), ("P4", 24), ("P7", 16), ("P8", 8)])
 def test_pbs_cluster_variant(engine, name, n_small):
     """The thread-block-cluster variant of the group kernel (one CTA per GLWE polynomial, Fourier
     digits exchanged through distributed shared memory; pbs_grp.cuh) is the default only at
@@ -298,7 +298,8 @@ def test_pbs_every_kernel_family(engine, name, n_small, plan):
 
 
 @pytest.mark.parametrize("k,N,b,l", [(1, 8192, 15, 2), (1, 1024, 12, 3), (1, 2048, 9, 3),
-                                     (2, 1024, 10, 2), (1, 4096, 11, 2), (1, 2048, 16, 2)])
+                                     (2, 1024, 10, 2), (1, 4096, 11, 2), (1, 2048, 16, 2),
+                                     (1, 16384, 15, 2), (1, 16384, 22, 1), (1, 16384, 11, 3)])
 def test_pbs_v4_multi_level(engine, k, N, b, l):
     """v4 with l >= 2: Fourier accumulators parked in tensor memory between levels; 32-bit
     (b*l <= 31) and 64-bit (b*l > 31) decomposition states."""
@@ -311,6 +312,13 @@ def test_pbs_v4_rounds_and_tail(engine):
     over all CTAs) with the small dimension cut so that the oracle finishes in seconds."""
     ks = keyset("TOY1024", n_override=6)  # k = 1, N = 1024: 8 ciphertexts per CTA
     _pbs_check(engine, ks, 148 * 8 + 148 * 3 + 17, 3, use_ks=False)
+
+
+def test_pbs_v4_cluster_rounds_and_tail(engine):
+    """N = 16384 (one polynomial per SM, the two CTAs of a cluster per ciphertext): more ciphertexts
+    than one wave of clusters plus a ragged tail, P8's decomposition, small dimension cut to 3."""
+    ks = keyset("P8", n_override=3)
+    _pbs_check(engine, ks, 74 * 2 + 29, 4, use_ks=False)
 
 
 def test_pbs_empty_batch(engine):
