@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline budget")
     ap.add_argument("--pbs-plan", type=int, default=0,
                     help="test hook: pin the PBS kernel family (see include/concrete_b200.h)")
+    ap.add_argument("--v4-alt", type=int, default=0, help="tuning hook (concrete_b200_set_v4_alt)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true",
@@ -456,6 +457,8 @@ def run_ours(args):
     lib = eng.lib
     if args.pbs_plan:
         lib.concrete_b200_set_pbs_plan(args.pbs_plan)
+    if args.v4_alt:
+        lib.concrete_b200_set_v4_alt(args.v4_alt)
     p = PARAMS[args.workload]
     S = args.samples
 

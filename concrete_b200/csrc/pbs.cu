@@ -365,7 +365,10 @@ Family key_family(u32 k, u32 N, u32 level) {
   if (plan == PLAN_GENERIC || plan == PLAN_GRP || plan == PLAN_CLUSTER) return FAM_GENERIC;
   if (plan == PLAN_V4 && cb_pbs_v4_shape(k, N)) return FAM_V4;
   if (use_w32(k, N, level)) return FAM_W32;
-  if (cb_pbs_v4_shape(k, N)) return FAM_V4;
+  // k = 2 (P4): measured on B200 the group kernel is ahead of v4 at every batch size (16 384
+  // samples: 243 vs 256 ms; 64 samples: 3.0 vs 5.5 ms - one warp per polynomial is a long
+  // dependent chain), so v4 stays opt-in there (plan 4)
+  if (cb_pbs_v4_shape(k, N) && k == 1) return FAM_V4;
   return FAM_GENERIC;
 }
 

@@ -4,12 +4,17 @@
 #include "pbs_common.cuh"
 #include "sm100_prims.cuh"
 #include "pbs_v4.cuh"
+#include <atomic>
 
 namespace {
+
+// tuning hook (tools/ and tests only): alternative instantiations of the N = 16384 two-level kernel
+std::atomic<int> g_v4_alt{0};
 
 struct V4Variant {
   void (*one_level)(const PbsArgs);    // l = 1
   void (*multi_narrow)(const PbsArgs); // l >= 2, base_log * l <= 31 (32-bit decomposition states)
+  void (*two_narrow)(const PbsArgs);   // l == 2 known at compile time (P8), 32-bit states
   void (*multi_wide)(const PbsArgs);   // l >= 2, base_log * l  > 31
   void (*convert)(double2 *, const double2 *, size_t);
   int threads, T, cpb, logm;
@@ -23,6 +28,7 @@ template <int K, int LOGN, int CPB, int RB, int NB, bool CLUSTER = false> V4Vari
   V4Variant v;
   v.one_level = v4::pbs_kernel_v4<C1, true, 1>;
   v.multi_narrow = v4::pbs_kernel_v4<CL, true, 0>;
+  v.two_narrow = v4::pbs_kernel_v4<CL, true, 2>;
   v.multi_wide = v4::pbs_kernel_v4<CL, false, 0>;
   v.convert = v4::bsk_convert_kernel_v4<C1>;
   v.threads = C1::THREADS;
@@ -46,12 +52,19 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   if (k == 1 && N == 2048) { v = make_v4<1, 11, 4, 8, 2>(); return true; }  // 128 + 64 KiB
   if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
-  if (k == 1 && N == 16384) { v = make_v4<1, 14, 1, 2, 3, true>(); return true; } // 128 + 96 KiB
+  if (k == 1 && N == 16384) { // 128 + 96 KiB
+    v = make_v4<1, 14, 1, 2, 3, true>();
+    const int alt = g_v4_alt.load();
+    if (alt == 1) v.two_narrow = v4::pbs_kernel_v4<v4::Cfg<1, 14, 4, 1, true, 2, 3, true, true>, true, 2>;
+    return true;
+  }
   if (k == 2 && N == 1024) { v = make_v4<2, 10, 5, 8, 2>(); return true; }  // 120 + 72 KiB
   return false;
 }
 
 } // namespace
+
+extern "C" void concrete_b200_set_v4_alt(int alt) { g_v4_alt.store(alt); }
 
 bool cb_pbs_v4_shape(u32 k, u32 N) {
   return (k == 1 && (N == 1024 || N == 2048 || N == 4096 || N == 8192 || N == 16384)) ||
@@ -101,7 +114,9 @@ void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out
   a.lut_count = lut_count;
   a.lut_stride = lut_stride;
   void (*kern)(const PbsArgs) =
-      level == 1 ? v.one_level : (base_log * level <= 31 ? v.multi_narrow : v.multi_wide);
+      level == 1 ? v.one_level
+                 : (base_log * level <= 31 ? (level == 2 ? v.two_narrow : v.multi_narrow)
+                                           : v.multi_wide);
   const size_t smem = level == 1 ? v.smem : v.smem_stash;
   CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int sms = 0;

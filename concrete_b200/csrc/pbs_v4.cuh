@@ -28,8 +28,12 @@ namespace v4 {
 using namespace sm100;
 
 template <int K_, int LOGN_, int LOGP_, int CPB_, bool STASH_, int RB_ = 4, int NB_ = 2,
-          bool CL_ = false>
+          bool CL_ = false, bool PACK_ = false>
 struct Cfg {
+  // PACK: see PACK2 in cmux().  Off by default: measured on B200 at P8 x 1024 it is slower (648 ms
+  // against 625 ms) although ptxas reports fewer spill bytes - the packing/unpacking integer work
+  // sits on the critical path of a phase in which all 16 warps of the SM wait for each other.
+  static constexpr bool PACK = PACK_;
   static constexpr int K = K_, LOGN = LOGN_, LOGM = LOGN_ - 1, M = 1 << LOGM, N = 2 * M;
   static constexpr int LOGP = LOGP_, P = 1 << LOGP_, T = M / P;
   // CL: the k+1 groups of ONE ciphertext are the k+1 CTAs of a thread-block cluster (one
@@ -370,7 +374,14 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
   const u32 base_log = ctrl->base_log, level = LV ? (u32)LV : ctrl->level;
 
   // ---- phase A: ct1_r = ACC_r * X^a - ACC_r, rounding, decomposition states
-  st_t st_re[P], st_im[P];
+  // PACK2 (two levels, 32-bit states): the first level's digits are taken right here and what is
+  // left of the two states of a point (the top digit plus a carry: <= 2^base_log each, and
+  // base_log <= 15 since 2 * base_log <= 31) is packed into ONE register, so 16 registers less
+  // are live across the first forward transform and product (ptxas: 532 -> 128 B of spills)
+  constexpr bool PACK2 = (LV == 2) && NARROW && C::PACK;
+  st_t st_re[PACK2 ? 1 : P], st_im[PACK2 ? 1 : P];
+  u32 pk[PACK2 ? P : 1];
+  double2 x[P];
   {
     const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5;
     const ulonglong2 *acc = reinterpret_cast<const ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
@@ -396,16 +407,35 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
         const u64 rb = (q & 1) ? src.x : src.y;
         const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
         const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
-        st_re[p] = (st_t)(closest_representable(rot_re - own_re[e], round_shift) >> state_shift);
-        st_im[p] = (st_t)(closest_representable(rot_im - own_im[e], round_shift) >> state_shift);
+        const st_t s_re = (st_t)(closest_representable(rot_re - own_re[e], round_shift) >> state_shift);
+        const st_t s_im = (st_t)(closest_representable(rot_im - own_im[e], round_shift) >> state_shift);
+        if constexpr (PACK2) {
+          const u32 mask = (1u << base_log) - 1u;
+          u32 a = (u32)s_re, b = (u32)s_im;
+          x[p].x = __int2double_rn((int)grp_decompose<u32>(a, mask, base_log));
+          x[p].y = __int2double_rn((int)grp_decompose<u32>(b, mask, base_log));
+          pk[p] = a | (b << 16);
+        } else {
+          st_re[p] = s_re;
+          st_im[p] = s_im;
+        }
       }
     }
   }
 
-  double2 x[P];
 #pragma unroll 1
   for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
-    {
+    if constexpr (PACK2) {
+      if (m > 0) {
+        const u32 mask = (1u << base_log) - 1u;
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+          u32 a = pk[p] & 0xFFFFu, b = pk[p] >> 16;
+          x[p].x = __int2double_rn((int)grp_decompose<u32>(a, mask, base_log));
+          x[p].y = __int2double_rn((int)grp_decompose<u32>(b, mask, base_log));
+        }
+      }
+    } else {
       const st_t mask = (st_t)(((u64)1 << base_log) - 1);
 #pragma unroll
       for (int p = 0; p < P; ++p) {

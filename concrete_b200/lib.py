@@ -59,6 +59,7 @@ SIGNATURES = {
     "concrete_b200_kernel_launches": (u64, []),
     "concrete_b200_set_pbs_plan": (None, [C.c_int]),
     "concrete_b200_set_ks_plan": (None, [C.c_int]),
+    "concrete_b200_set_v4_alt": (None, [C.c_int]),
 }
 
 # runtime wrapper layer, include/concrete_b200_runtime.h (MLIR memref ABI; host pointers)

@@ -198,6 +198,9 @@ uint64_t concrete_b200_kernel_launches(void);
  * tensor cores whenever exact. */
 void concrete_b200_set_pbs_plan(int plan);
 void concrete_b200_set_ks_plan(int plan);
+/* TUNING hook: alternative instantiations (key-ring geometry, state packing) of the N = 16384
+ * two-level v4 kernel, 0 = the default; same key layout, same results. */
+void concrete_b200_set_v4_alt(int alt);
 /* FP64 FMA peak probe: `blocks` CTAs x 256 threads x iters x 16 DFMA (32 flop) per thread;
  * bench.py times it with CUDA events for the roofline denominator. */
 void concrete_b200_fp64_peak(void *stream, uint32_t gpu_index, void *scratch, uint32_t blocks,
