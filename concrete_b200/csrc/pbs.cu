@@ -601,9 +601,10 @@ void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_ho
   const size_t polys = (size_t)n * level * (k + 1) * (k + 1);
   const size_t bytes = polys * N * sizeof(u64);
   if (bytes == 0) return;
-  CB_CHECK(cudaMemcpyAsync(dest, src_host, bytes,
-                           src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
-                           stream));
+  if (dest != src_host) // (the seeded-key path decompresses straight into dest: seeded.cu)
+    CB_CHECK(cudaMemcpyAsync(dest, src_host, bytes,
+                             src_on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice,
+                             stream));
   const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
   int sms = 0;
   CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));

@@ -69,6 +69,36 @@ class Engine:
         self.lib.cuda_synchronize_stream(self.stream, self.gpu)  # as context.h:110
         return dest
 
+    # ------------------------------------------------------------------ seeded keys
+    @staticmethod
+    def _halves(seed: int):
+        return seed & (2 ** 64 - 1), seed >> 64
+
+    def decompress_seeded_bsk(self, seeded: np.ndarray, n, k, level, N, seed: int,
+                              convert: bool = False) -> torch.Tensor:
+        """Seeded BSK (bodies, host) -> standard BSK on the device, or (convert=True) straight to
+        the Fourier key the PBS consumes; masks regenerated on the device from the 128-bit seed
+        (replaces Keys.cpp:193-213 + context.h:86-115)."""
+        seeded = np.ascontiguousarray(seeded, dtype=np.uint64)
+        assert seeded.size == n * level * (k + 1) * N
+        dest = torch.empty(n * level * (k + 1) ** 2 * N, dtype=torch.int64, device=self.device)
+        lo, hi = self._halves(seed)
+        f = (self.lib.cuda_convert_seeded_lwe_programmable_bootstrap_key_64 if convert
+             else self.lib.cuda_decompress_seeded_lwe_bootstrap_key_64)
+        f(self.stream, self.gpu, dest.data_ptr(), seeded.ctypes.data, n, k, level, N, lo, hi)
+        self.lib.cuda_synchronize_stream(self.stream, self.gpu)  # host bodies may go away now
+        return dest
+
+    def decompress_seeded_ksk(self, seeded: np.ndarray, n_in, n_out, level, seed: int) -> torch.Tensor:
+        seeded = np.ascontiguousarray(seeded, dtype=np.uint64)
+        assert seeded.size == n_in * level
+        dest = torch.empty(n_in * level * (n_out + 1), dtype=torch.int64, device=self.device)
+        lo, hi = self._halves(seed)
+        self.lib.cuda_decompress_seeded_lwe_keyswitch_key_64(
+            self.stream, self.gpu, dest.data_ptr(), seeded.ctypes.data, n_in, n_out, level, lo, hi)
+        self.lib.cuda_synchronize_stream(self.stream, self.gpu)
+        return dest
+
     # ------------------------------------------------------------------ keyswitch
     def keyswitch(self, cts: torch.Tensor, ksk: torch.Tensor, n_in: int, n_out: int,
                   base_log: int, level: int, out: torch.Tensor | None = None,

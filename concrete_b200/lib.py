@@ -55,6 +55,10 @@ SIGNATURES = {
     "cuda_keyswitch_lwe_ciphertext_vector_64_legacy": (None, [vp, u32, vp, vp, vp, u32, u32, u32, u32, u32]),
     "cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64": (
         None, [vp, u32, vp, vp, vp, vp, vp, vp, i8p, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "cuda_decompress_seeded_lwe_bootstrap_key_64": (None, [vp, u32, vp, vp, u32, u32, u32, u32, u64, u64]),
+    "cuda_decompress_seeded_lwe_keyswitch_key_64": (None, [vp, u32, vp, vp, u32, u32, u32, u64, u64]),
+    "cuda_convert_seeded_lwe_programmable_bootstrap_key_64": (
+        None, [vp, u32, vp, vp, u32, u32, u32, u32, u64, u64]),
     "concrete_b200_version": (C.c_char_p, []),
     "concrete_b200_kernel_launches": (u64, []),
     "concrete_b200_set_pbs_plan": (None, [C.c_int]),

@@ -190,6 +190,30 @@ void cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
 /* Library self-description (not in the reference): build tag + last-launch kernel counter,
  * used by bench.py to report `gpu_launches`. */
 const char *concrete_b200_version(void);
+/* ---- seeded (compressed) keys, decompressed on the device ----------------
+ * Replace concrete_cpu_decompress_seeded_lwe_bootstrap_key_u64
+ * (backends/concrete-cpu/implementation/src/c_api/bootstrap.rs:169-237) and
+ * concrete_cpu_decompress_seeded_lwe_keyswitch_key_u64 (c_api/keyswitch.rs) + the full-key upload
+ * of RuntimeContext::get_{bsk,ksk}_gpu (context.h:86-145): the caller passes the seeded key (bodies
+ * only: n*l*(k+1)*N words, resp. n_in*l words; host or device pointer) and the 128-bit
+ * compression seed (Uint128 little_endian_bytes as two u64 halves); the masks are regenerated on
+ * the device with the reference's AES-128-CTR generator (concrete-csprng).  `dest` is a device
+ * buffer of the full key size; the _convert_ form leaves the private Fourier layout in it, as
+ * cuda_convert_lwe_programmable_bootstrap_key_64 does. */
+void cuda_decompress_seeded_lwe_bootstrap_key_64(void *stream, uint32_t gpu_index, void *dest,
+                                                 const void *seeded_bsk, uint32_t input_lwe_dim,
+                                                 uint32_t glwe_dim, uint32_t level_count,
+                                                 uint32_t polynomial_size, uint64_t seed_lo,
+                                                 uint64_t seed_hi);
+void cuda_decompress_seeded_lwe_keyswitch_key_64(void *stream, uint32_t gpu_index, void *dest,
+                                                 const void *seeded_ksk, uint32_t lwe_dim_in,
+                                                 uint32_t lwe_dim_out, uint32_t level_count,
+                                                 uint64_t seed_lo, uint64_t seed_hi);
+void cuda_convert_seeded_lwe_programmable_bootstrap_key_64(
+    void *stream, uint32_t gpu_index, void *dest, const void *seeded_bsk, uint32_t input_lwe_dim,
+    uint32_t glwe_dim, uint32_t level_count, uint32_t polynomial_size, uint64_t seed_lo,
+    uint64_t seed_hi);
+
 uint64_t concrete_b200_kernel_launches(void);
 /* TEST hooks (not in the reference): pin the kernel family so that the tests keep every kernel
  * covered.  PBS: 0 automatic, 1 first generic kernel, 2 group kernel, 3 cluster kernel, 4 v4

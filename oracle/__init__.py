@@ -295,3 +295,67 @@ def gen_bsk(lwe_key, glwe_key, k, N, base_log, level, sigma, seed) -> np.ndarray
     lib().orc_gen_bsk(_p(bsk), _p(lwe_key), _p(glwe_key), n, k, C.c_size_t(N), base_log, level,
                       C.c_double(sigma), C.c_uint64(seed))
     return bsk
+
+
+def gen_ksk_masks(key_in, key_out, base_log, level, sigma, seed, masks) -> np.ndarray:
+    """gen_ksk with the mask elements given ([n_in][level][n_out]): seeded-key tests."""
+    n_in, n_out = len(key_in), len(key_out)
+    assert masks.size == n_in * level * n_out
+    ksk = np.empty(n_in * level * (n_out + 1), dtype=np.uint64)
+    lib().orc_gen_ksk_masks(_p(ksk), _p(key_in), _p(key_out), n_in, n_out, base_log, level,
+                            C.c_double(sigma), C.c_uint64(seed), _p(np.ascontiguousarray(masks)))
+    return ksk
+
+
+def gen_bsk_masks(lwe_key, glwe_key, k, N, base_log, level, sigma, seed, masks) -> np.ndarray:
+    """gen_bsk with the mask polynomials given ([n][level][k+1][k][N]): seeded-key tests."""
+    n = len(lwe_key)
+    assert masks.size == n * level * (k + 1) * k * N
+    bsk = np.empty(n * level * (k + 1) ** 2 * N, dtype=np.uint64)
+    lib().orc_gen_bsk_masks(_p(bsk), _p(lwe_key), _p(glwe_key), n, k, C.c_size_t(N), base_log, level,
+                            C.c_double(sigma), C.c_uint64(seed), _p(np.ascontiguousarray(masks)))
+    return bsk
+
+
+# ---------------------------------------------------------------- seeded keys (csprng_oracle.cpp)
+def _seed_halves(seed: int):
+    return C.c_uint64(seed & (2 ** 64 - 1)), C.c_uint64(seed >> 64)
+
+
+def aes128_encrypt(key: bytes, block: bytes) -> bytes:
+    out = (C.c_uint8 * 16)()
+    lib().orc_aes128_encrypt(key, block, out)
+    return bytes(out)
+
+
+def csprng_bytes(seed: int, first_byte: int, count: int) -> np.ndarray:
+    """Bytes [first_byte, first_byte + count) a fresh generator of `seed` (u128) outputs."""
+    out = np.empty(count, dtype=np.uint8)
+    lo, hi = _seed_halves(seed)
+    lib().orc_csprng_bytes(_p(out, np.uint8), C.c_uint64(first_byte), C.c_uint64(count), lo, hi)
+    return out
+
+
+def csprng_u64(seed: int, first_word: int, count: int) -> np.ndarray:
+    out = np.empty(count, dtype=np.uint64)
+    lo, hi = _seed_halves(seed)
+    lib().orc_csprng_fill_u64(_p(out), C.c_uint64(first_word), C.c_uint64(count), lo, hi)
+    return out
+
+
+def decompress_seeded_bsk(seeded, n, k, N, level, seed: int) -> np.ndarray:
+    assert seeded.size == n * level * (k + 1) * N
+    out = np.empty(n * level * (k + 1) ** 2 * N, dtype=np.uint64)
+    lo, hi = _seed_halves(seed)
+    lib().orc_decompress_seeded_bsk(_p(out), _p(np.ascontiguousarray(seeded)), n, k, C.c_size_t(N),
+                                    level, lo, hi)
+    return out
+
+
+def decompress_seeded_ksk(seeded, n_in, n_out, level, seed: int) -> np.ndarray:
+    assert seeded.size == n_in * level
+    out = np.empty(n_in * level * (n_out + 1), dtype=np.uint64)
+    lo, hi = _seed_halves(seed)
+    lib().orc_decompress_seeded_ksk(_p(out), _p(np.ascontiguousarray(seeded)), n_in, n_out, level,
+                                    lo, hi)
+    return out

@@ -606,9 +606,20 @@ void orc_lwe_decrypt_batch(u64 *plaintexts, const u64 *ct, const u64 *key, unsig
 
 // KSK: block i, memory level index j <-> level l-j, plaintext
 // s_in[i] << (64 - b*level)   (lwe_keyswitch_key_generation.rs:161-172)
+// `masks` (optional, [n_in][l][n_out]): mask elements to use instead of the harness RNG's — the
+// seeded-key tests pass the compression generator's stream (oracle/csprng_oracle.cpp) here, as
+// generate_seeded_lwe_keyswitch_key does (lwe_keyswitch_key_generation.rs, seeded variant).
+void orc_gen_ksk_masks(u64 *ksk, const u64 *key_in, const u64 *key_out, unsigned n_in,
+                       unsigned n_out, unsigned base_log, unsigned level_count, double sigma,
+                       u64 seed, const u64 *masks);
 void orc_gen_ksk(u64 *ksk, const u64 *key_in, const u64 *key_out, unsigned n_in,
                  unsigned n_out, unsigned base_log, unsigned level_count, double sigma,
                  u64 seed) {
+  orc_gen_ksk_masks(ksk, key_in, key_out, n_in, n_out, base_log, level_count, sigma, seed, nullptr);
+}
+void orc_gen_ksk_masks(u64 *ksk, const u64 *key_in, const u64 *key_out, unsigned n_in,
+                       unsigned n_out, unsigned base_log, unsigned level_count, double sigma,
+                       u64 seed, const u64 *masks) {
   const size_t out_size = (size_t)n_out + 1;
 #pragma omp parallel for schedule(static)
   for (long i = 0; i < (long)n_in; ++i) {
@@ -618,8 +629,10 @@ void orc_gen_ksk(u64 *ksk, const u64 *key_in, const u64 *key_out, unsigned n_in,
       u64 pt = key_in[i] << (64 - base_log * level);
       u64 *c = ksk + ((size_t)i * level_count + j) * out_size;
       u64 body = pt + r.noise(sigma);
+      const u64 *given = masks ? masks + ((size_t)i * level_count + j) * n_out : nullptr;
       for (unsigned o = 0; o < n_out; ++o) {
-        c[o] = r.next();
+        const u64 drawn = r.next(); // drawn either way: the noise stream does not depend on `masks`
+        c[o] = given ? given[o] : drawn;
         body += c[o] * key_out[o];
       }
       c[n_out] = body;
@@ -631,9 +644,19 @@ void orc_gen_ksk(u64 *ksk, const u64 *key_in, const u64 *key_out, unsigned n_in,
 // layout [n][l (memory m <-> level l-m)][k+1 rows][k+1 polys][N]
 // factor = (-s_i) << (64 - b*level); row r<k encrypts S_r*factor, last row encrypts
 // -factor in coefficient 0  (ggsw_encryption.rs:20-44,320-372).
+// `masks` (optional, [n][l][k+1 rows][k][N]): as for orc_gen_ksk_masks
+// (generate_seeded_lwe_bootstrap_key, c_api/bootstrap.rs:120-165).
+void orc_gen_bsk_masks(u64 *bsk, const u64 *lwe_key, const u64 *glwe_key, unsigned n, unsigned k,
+                       size_t N, unsigned base_log, unsigned level_count, double sigma, u64 seed,
+                       const u64 *masks);
 void orc_gen_bsk(u64 *bsk, const u64 *lwe_key /*n*/, const u64 *glwe_key /*k*N*/,
                  unsigned n, unsigned k, size_t N, unsigned base_log,
                  unsigned level_count, double sigma, u64 seed) {
+  orc_gen_bsk_masks(bsk, lwe_key, glwe_key, n, k, N, base_log, level_count, sigma, seed, nullptr);
+}
+void orc_gen_bsk_masks(u64 *bsk, const u64 *lwe_key /*n*/, const u64 *glwe_key /*k*N*/,
+                       unsigned n, unsigned k, size_t N, unsigned base_log,
+                       unsigned level_count, double sigma, u64 seed, const u64 *masks) {
   const NegFft &fft = get_plan(N);
   const size_t gs = k + 1;
   const long rows = (long)n * level_count * gs;
@@ -660,7 +683,11 @@ void orc_gen_bsk(u64 *bsk, const u64 *lwe_key /*n*/, const u64 *glwe_key /*k*N*/
       // mask + <mask, key>
       for (size_t p = 0; p < k; ++p) {
         u64 *a = row + p * N;
-        for (size_t c = 0; c < N; ++c) a[c] = rng.next();
+        const u64 *given = masks ? masks + ((size_t)idx * k + p) * N : nullptr;
+        for (size_t c = 0; c < N; ++c) {
+          const u64 drawn = rng.next();
+          a[c] = given ? given[c] : drawn;
+        }
         negacyclic_mul_binary(prod.data(), a, glwe_key + p * N, N, fft);
         for (size_t c = 0; c < N; ++c) body[c] += prod[c];
       }

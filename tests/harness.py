@@ -17,14 +17,32 @@ from concrete_b200.params import PARAMS, TfheParams  # noqa: E402
 class KeySet:
     """One big (GLWE-derived) key, one small key, one KSK, one BSK — all seeded."""
 
-    def __init__(self, p: TfheParams, seed: int = 42, fourier_oracle: bool = True, n_override=None):
+    def __init__(self, p: TfheParams, seed: int = 42, fourier_oracle: bool = True, n_override=None,
+                 compression_seeds=None):
+        """`compression_seeds` = (ksk_seed, bsk_seed), two u128: generate SEEDED keys — the masks
+        are the reference CSPRNG's stream for that seed (oracle/csprng_oracle.cpp) and
+        `seeded_ksk` / `seeded_bsk` hold the bodies only, as Concrete ships them
+        (generate_seeded_lwe_{keyswitch,bootstrap}_key); `ksk` / `bsk` are the full keys."""
         if n_override is not None:
             p = TfheParams(**{**p.__dict__, "n": n_override, "name": f"{p.name}_n{n_override}"})
         self.p = p
         self.sk_small = orc.gen_binary_key(p.n, seed)
         self.sk_glwe = orc.gen_binary_key(p.k * p.N, seed + 1)  # == big LWE key (into_lwe_secret_key)
-        self.ksk = orc.gen_ksk(self.sk_glwe, self.sk_small, p.b_ks, p.l_ks, p.sigma_lwe, seed + 2)
-        self.bsk = orc.gen_bsk(self.sk_small, self.sk_glwe, p.k, p.N, p.b, p.l, p.sigma_glwe, seed + 3)
+        if compression_seeds is None:
+            self.ksk = orc.gen_ksk(self.sk_glwe, self.sk_small, p.b_ks, p.l_ks, p.sigma_lwe, seed + 2)
+            self.bsk = orc.gen_bsk(self.sk_small, self.sk_glwe, p.k, p.N, p.b, p.l, p.sigma_glwe, seed + 3)
+        else:
+            self.ksk_seed, self.bsk_seed = compression_seeds
+            km = orc.csprng_u64(self.ksk_seed, 0, p.big_n * p.l_ks * p.n)
+            self.ksk = orc.gen_ksk_masks(self.sk_glwe, self.sk_small, p.b_ks, p.l_ks, p.sigma_lwe,
+                                         seed + 2, km)
+            bm = orc.csprng_u64(self.bsk_seed, 0, p.n * p.l * (p.k + 1) * p.k * p.N)
+            self.bsk = orc.gen_bsk_masks(self.sk_small, self.sk_glwe, p.k, p.N, p.b, p.l,
+                                         p.sigma_glwe, seed + 3, bm)
+            self.seeded_ksk = np.ascontiguousarray(
+                self.ksk.reshape(p.big_n * p.l_ks, p.n + 1)[:, p.n])
+            self.seeded_bsk = np.ascontiguousarray(
+                self.bsk.reshape(p.n * p.l * (p.k + 1), p.k + 1, p.N)[:, p.k]).reshape(-1)
         self.fbsk = orc.bsk_to_fourier(self.bsk, p.n, p.k, p.l, p.N) if fourier_oracle else None
 
     def encrypt_big(self, msgs: np.ndarray, bits: int, seed: int = 7) -> np.ndarray:

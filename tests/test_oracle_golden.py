@@ -281,3 +281,64 @@ def test_timed_cpu_baseline_agrees_with_the_oracle(name, bits, num):
     got = orc.fast_bootstrap(ref_mid, lut, None, ks.fbsk, p.n, p.k, p.N, p.b, p.l)
     assert np.array_equal(ks.decrypt_big(got, bits), ks.decrypt_big(ref, bits))
     assert phase_distance(ks, got, ref).max() <= phase_tolerance(p)
+
+
+# ------------------------------------------------------------------ seeded keys
+def test_aes128_fips197_vectors():
+    """The reference's own known-answer test (concrete-csprng/src/generators/implem/soft/
+    block_cipher.rs:90-112: FIPS-197 appendix C.1) and the appendix B example."""
+    assert orc.aes128_encrypt(bytes(range(16)), bytes.fromhex("00112233445566778899aabbccddeeff")) \
+        == bytes.fromhex("69c4e0d86a7b0430d8cdb78070b4c55a")
+    assert orc.aes128_encrypt(bytes.fromhex("2b7e151628aed2a6abf7158809cf4f3c"),
+                              bytes.fromhex("3243f6a8885a308d313198a2e0370734")) \
+        == bytes.fromhex("3925841d02dc09fbdc118597196a0b32")
+
+
+def test_csprng_stream_definition():
+    """Byte q of a fresh generator is byte (1 + q) of the table AES_seed(counter) with key and
+    counter as little-endian u128 (block_cipher.rs:16-36, generic.rs:60-72, index.rs:28-31),
+    checked against an independent AES (the `cryptography` package) when it is importable; and
+    forked children read consecutive ranges of the parent's table (generic.rs:124-170,
+    aes_ctr_generic_test::prop_fork): any split of a range equals the range."""
+    seed = 0x0123456789ABCDEF_FEDCBA9876543210
+    got = orc.csprng_bytes(seed, 0, 1000).tobytes()
+    try:
+        from cryptography.hazmat.primitives.ciphers import Cipher, algorithms, modes
+        enc = Cipher(algorithms.AES(seed.to_bytes(16, "little")), modes.ECB()).encryptor()
+        table = b"".join(enc.update(i.to_bytes(16, "little")) for i in range(64))
+        assert got == table[1:1001]
+    except ImportError:
+        pass
+    block0 = orc.aes128_encrypt(seed.to_bytes(16, "little"), (0).to_bytes(16, "little"))
+    assert got[:15] == block0[1:]
+    for a, b in ((1, 14), (15, 1), (16, 17), (333, 500)):
+        assert orc.csprng_bytes(seed, a, b).tobytes() == got[a:a + b]
+    words = orc.csprng_u64(seed, 5, 40)
+    assert [int(w) for w in words] == [int.from_bytes(got[8 * (5 + i): 8 * (6 + i)], "little")
+                                       for i in range(40)]
+
+
+@pytest.mark.parametrize("name", ["TOY512", "TOY256K2"])
+def test_seeded_key_decompression_roundtrip(name):
+    """generate_seeded_* / decompress_seeded_* (c_api/bootstrap.rs:120-237): a key generated with
+    the compression generator's masks, stripped to its bodies and decompressed again is the same
+    key word for word, masks in generator order (GGSW, level, row, polynomial); and it works: a
+    keyswitch + PBS through the decompressed keys decrypts."""
+    from harness import KeySet, PARAMS, expand_lut, trivial_glwe
+    p = PARAMS[name]
+    ks = KeySet(p, seed=42, fourier_oracle=False, compression_seeds=(0xA5A5_0000_1234, 2 ** 127 + 99))
+    rows = p.n * p.l * (p.k + 1)
+    full = ks.bsk.reshape(rows, p.k + 1, p.N)
+    assert np.array_equal(full[:, :p.k].reshape(-1), orc.csprng_u64(ks.bsk_seed, 0, rows * p.k * p.N))
+    assert np.array_equal(orc.decompress_seeded_bsk(ks.seeded_bsk, p.n, p.k, p.N, p.l, ks.bsk_seed),
+                          ks.bsk)
+    assert np.array_equal(orc.decompress_seeded_ksk(ks.seeded_ksk, p.big_n, p.n, p.l_ks, ks.ksk_seed),
+                          ks.ksk)
+    bits, num = 2, 9
+    msgs = (np.arange(num) % (1 << bits)).astype(np.uint64)
+    table = (np.arange(1 << bits) * 3 % (1 << bits)).astype(np.uint64)
+    lut = trivial_glwe(expand_lut(table, p.N, bits), p.k)
+    mid = orc.keyswitch(ks.encrypt_big(msgs, bits), ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks)
+    fbsk = orc.bsk_to_fourier(ks.bsk, p.n, p.k, p.l, p.N)
+    out = orc.bootstrap(mid, lut, None, fbsk, p.n, p.k, p.N, p.b, p.l)
+    assert np.array_equal(ks.decrypt_big(out, bits), table[msgs])
