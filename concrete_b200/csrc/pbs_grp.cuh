@@ -88,6 +88,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   const u32 n = a.n, base_log = a.base_log, level = a.level;
   const st_t mask = (st_t)(((u64)1 << base_log) - 1);
   const u32 round_shift = 64 - base_log * level - 1;
+  const bool fast1 = (level == 1); // uniform over the grid
   const u32 state_shift = 64 - base_log * level;
   const double2 *__restrict__ tw = a.tw;
   const size_t out_size = (size_t)K * N + 1;
@@ -135,8 +136,14 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
         const u64 rb = (q & 1) ? src.x : src.y;
         const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
         const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
-        st_re[p] = (st_t)(closest_representable(rot_re - own.x, round_shift) >> state_shift);
-        st_im[p] = (st_t)(closest_representable(rot_im - own.y, round_shift) >> state_shift);
+        if (fast1) { // one level: rounding + balanced digit from the high word (pbs_v4.cuh FAST1)
+          const u32 kshift = 32 - base_log, half_m1 = (1u << (kshift - 1)) - 1u;
+          st_re[p] = (st_t)(u32)(-((int)(half_m1 - (u32)((rot_re - own.x) >> 32)) >> kshift));
+          st_im[p] = (st_t)(u32)(-((int)(half_m1 - (u32)((rot_im - own.y) >> 32)) >> kshift));
+        } else {
+          st_re[p] = (st_t)(closest_representable(rot_re - own.x, round_shift) >> state_shift);
+          st_im[p] = (st_t)(closest_representable(rot_im - own.y, round_shift) >> state_shift);
+        }
       }
       double2 oacc[P];
 #pragma unroll
@@ -153,8 +160,10 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           double2 x[P];
 #pragma unroll
           for (int p = 0; p < P; ++p) {
-            x[p].x = __int2double_rn((int)(u32)grp_decompose<st_t>(st_re[p], mask, base_log));
-            x[p].y = __int2double_rn((int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
+            x[p].x = __int2double_rn(fast1 ? (int)(u32)st_re[p]
+                                           : (int)(u32)grp_decompose<st_t>(st_re[p], mask, base_log));
+            x[p].y = __int2double_rn(fast1 ? (int)(u32)st_im[p]
+                                           : (int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
           }
           cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw, bar_id);
           cbfft::group_sync<T>(bar_id); // last exchange of the transform fully read

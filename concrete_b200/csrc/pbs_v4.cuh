@@ -379,7 +379,14 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
   // base_log <= 15 since 2 * base_log <= 31) is packed into ONE register, so 16 registers less
   // are live across the first forward transform and product (ptxas: 532 -> 128 B of spills)
   constexpr bool PACK2 = (LV == 2) && NARROW && C::PACK;
-  st_t st_re[PACK2 ? 1 : P], st_im[PACK2 ? 1 : P];
+  // FAST1 (one level): closest_representable + the balanced digit straight from the HIGH word of
+  // ct1 in two integer instructions (the rounding bit 63 - base_log lies in the high word for every
+  // base_log <= 31; same derivation as pbs_w32_v3.cuh neg_digit_l1_k: round-half-up of x is minus
+  // round-half-down of -x, taken by an arithmetic shift; the tie lands on +B/2 as in
+  // decomposer.rs:23-47 + iter.rs:121-133).  ncu on P7 (profiles/r2_v4_P7_ncu.txt): phase A was
+  // 15.7 % of the CMUX, bound by the integer pipe.
+  constexpr bool FAST1 = (LV == 1);
+  st_t st_re[(PACK2 || FAST1) ? 1 : P], st_im[(PACK2 || FAST1) ? 1 : P];
   u32 pk[PACK2 ? P : 1];
   double2 x[P];
   {
@@ -407,6 +414,14 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
         const u64 rb = (q & 1) ? src.x : src.y;
         const u64 rot_re = (q == 2 || q == 3) ? (u64)0 - ra : ra;
         const u64 rot_im = (q == 1 || q == 2) ? (u64)0 - rb : rb;
+        if constexpr (FAST1) {
+          const u32 kshift = 32 - base_log;
+          const u32 half_m1 = (1u << (kshift - 1)) - 1u;
+          const u32 h_re = (u32)((rot_re - own_re[e]) >> 32), h_im = (u32)((rot_im - own_im[e]) >> 32);
+          x[p].x = -__int2double_rn((int)(half_m1 - h_re) >> kshift);
+          x[p].y = -__int2double_rn((int)(half_m1 - h_im) >> kshift);
+          continue;
+        }
         const st_t s_re = (st_t)(closest_representable(rot_re - own_re[e], round_shift) >> state_shift);
         const st_t s_im = (st_t)(closest_representable(rot_im - own_im[e], round_shift) >> state_shift);
         if constexpr (PACK2) {
@@ -425,7 +440,9 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
 
 #pragma unroll 1
   for (u32 m = 0; m < level; ++m) { // memory level index m <-> level l-m (ggsw.rs:231-245)
-    if constexpr (PACK2) {
+    if constexpr (FAST1) {
+      // digits taken in phase A
+    } else if constexpr (PACK2) {
       if (m > 0) {
         const u32 mask = (1u << base_log) - 1u;
 #pragma unroll

@@ -25,13 +25,20 @@
 namespace mlir {
 namespace concretelang {
 
+// A key is held either in full or in SEEDED form (bodies + the 128-bit compression seed, as the
+// keyset ships it: Common/Keys.cpp:193-213); `len` is always the FULL key's word count, which is
+// what sizes the device buffer (context.h:101-105).
 struct HostKeyswitchKey {
   const uint64_t *data;
-  size_t len; // words
+  size_t len; // words of the full key
+  bool seeded = false;
+  uint64_t seed_lo = 0, seed_hi = 0;
 };
 struct HostBootstrapKey {
-  const uint64_t *data; // standard domain [n][l][k+1][k+1][N]
-  size_t len;           // words
+  const uint64_t *data; // standard domain [n][l][k+1][k+1][N], or seeded [n][l][k+1][N]
+  size_t len;           // words of the full key
+  bool seeded = false;
+  uint64_t seed_lo = 0, seed_hi = 0;
 };
 
 // grow-only device buffer owned by a GpuSlot
@@ -106,6 +113,25 @@ typedef struct RuntimeContext {
     return host_bsks.size() - 1;
   }
 
+  // seeded forms: the masks are regenerated on each device (csrc/seeded.cu) instead of
+  // decompressing on the host and uploading the full key
+  size_t add_seeded_keyswitch_key(const uint64_t *bodies, size_t full_len, uint64_t seed_lo,
+                                  uint64_t seed_hi) {
+    size_t id = add_keyswitch_key(bodies, full_len);
+    host_ksks[id].seeded = true;
+    host_ksks[id].seed_lo = seed_lo;
+    host_ksks[id].seed_hi = seed_hi;
+    return id;
+  }
+  size_t add_seeded_bootstrap_key(const uint64_t *bodies, size_t full_len, uint64_t seed_lo,
+                                  uint64_t seed_hi) {
+    size_t id = add_bootstrap_key(bodies, full_len);
+    host_bsks[id].seeded = true;
+    host_bsks[id].seed_lo = seed_lo;
+    host_bsks[id].seed_hi = seed_hi;
+    return id;
+  }
+
   virtual const uint64_t *keyswitch_key_buffer(size_t keyId) { return host_ksks[keyId].data; }
 
   // context.h:86-115
@@ -117,9 +143,14 @@ typedef struct RuntimeContext {
     const HostBootstrapKey &bsk = host_bsks[bsk_idx];
     size_t bsk_gpu_buffer_size = bsk.len * sizeof(double);
     void *bsk_gpu_tmp = cuda_malloc_async(bsk_gpu_buffer_size, stream, gpu_idx);
-    cuda_convert_lwe_programmable_bootstrap_key_64(stream, gpu_idx, bsk_gpu_tmp,
-                                                   const_cast<uint64_t *>(bsk.data),
-                                                   input_lwe_dim, glwe_dim, level, poly_size);
+    if (bsk.seeded)
+      cuda_convert_seeded_lwe_programmable_bootstrap_key_64(stream, gpu_idx, bsk_gpu_tmp, bsk.data,
+                                                            input_lwe_dim, glwe_dim, level,
+                                                            poly_size, bsk.seed_lo, bsk.seed_hi);
+    else
+      cuda_convert_lwe_programmable_bootstrap_key_64(stream, gpu_idx, bsk_gpu_tmp,
+                                                     const_cast<uint64_t *>(bsk.data),
+                                                     input_lwe_dim, glwe_dim, level, poly_size);
     cuda_synchronize_stream(stream, gpu_idx);
     bsk_gpu[gpu_idx][bsk_idx] = bsk_gpu_tmp;
     return bsk_gpu_tmp;
@@ -128,17 +159,19 @@ typedef struct RuntimeContext {
   // context.h:117-145
   void *get_ksk_gpu(uint32_t level, uint32_t input_lwe_dim, uint32_t output_lwe_dim,
                     uint32_t gpu_idx, void *stream, uint32_t ksk_idx) {
-    (void)level;
-    (void)input_lwe_dim;
-    (void)output_lwe_dim;
     if (ksk_gpu[gpu_idx][ksk_idx] != nullptr) return ksk_gpu[gpu_idx][ksk_idx];
     const std::lock_guard<std::mutex> guard(*ksk_gpu_mutex[gpu_idx]);
     if (ksk_gpu[gpu_idx][ksk_idx] != nullptr) return ksk_gpu[gpu_idx][ksk_idx];
     const HostKeyswitchKey &ksk = host_ksks[ksk_idx];
     size_t ksk_buffer_size = sizeof(uint64_t) * ksk.len;
     void *ksk_gpu_tmp = cuda_malloc_async(ksk_buffer_size, stream, gpu_idx);
-    cuda_memcpy_async_to_gpu(ksk_gpu_tmp, const_cast<uint64_t *>(ksk.data), ksk_buffer_size,
-                             stream, gpu_idx);
+    if (ksk.seeded)
+      cuda_decompress_seeded_lwe_keyswitch_key_64(stream, gpu_idx, ksk_gpu_tmp, ksk.data,
+                                                  input_lwe_dim, output_lwe_dim, level, ksk.seed_lo,
+                                                  ksk.seed_hi);
+    else
+      cuda_memcpy_async_to_gpu(ksk_gpu_tmp, const_cast<uint64_t *>(ksk.data), ksk_buffer_size,
+                               stream, gpu_idx);
     cuda_synchronize_stream(stream, gpu_idx);
     ksk_gpu[gpu_idx][ksk_idx] = ksk_gpu_tmp;
     return ksk_gpu_tmp;

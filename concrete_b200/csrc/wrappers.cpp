@@ -234,6 +234,18 @@ uint64_t concrete_b200_context_add_ksk(void *ctx, const uint64_t *data, uint64_t
 uint64_t concrete_b200_context_add_bsk(void *ctx, const uint64_t *data, uint64_t len) {
   return static_cast<RuntimeContext *>(ctx)->add_bootstrap_key(data, len);
 }
+uint64_t concrete_b200_context_add_seeded_ksk(void *ctx, const uint64_t *bodies,
+                                              uint64_t full_len_words, uint64_t seed_lo,
+                                              uint64_t seed_hi) {
+  return static_cast<RuntimeContext *>(ctx)->add_seeded_keyswitch_key(bodies, full_len_words,
+                                                                       seed_lo, seed_hi);
+}
+uint64_t concrete_b200_context_add_seeded_bsk(void *ctx, const uint64_t *bodies,
+                                              uint64_t full_len_words, uint64_t seed_lo,
+                                              uint64_t seed_hi) {
+  return static_cast<RuntimeContext *>(ctx)->add_seeded_bootstrap_key(bodies, full_len_words,
+                                                                       seed_lo, seed_hi);
+}
 void concrete_b200_context_set_num_gpus(void *ctx, int n) {
   RuntimeContext *c = static_cast<RuntimeContext *>(ctx);
   if (n >= 1 && c->device_base + n <= c->num_devices) c->active_devices = n;

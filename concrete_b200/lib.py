@@ -74,6 +74,8 @@ SIGNATURES.update({
     "concrete_b200_context_destroy": (None, [vp]),
     "concrete_b200_context_add_ksk": (u64, [vp, vp, u64]),
     "concrete_b200_context_add_bsk": (u64, [vp, vp, u64]),
+    "concrete_b200_context_add_seeded_ksk": (u64, [vp, vp, u64, u64, u64]),
+    "concrete_b200_context_add_seeded_bsk": (u64, [vp, vp, u64, u64, u64]),
     "concrete_b200_context_set_num_gpus": (None, [vp, C.c_int]),
     "concrete_b200_context_set_device_base": (None, [vp, C.c_int]),
     "memref_batched_keyswitch_lwe_cuda_u64": (None, _m2 + _m2 + [u32, u32, u32, u32, u32, vp]),

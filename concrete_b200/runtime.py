@@ -47,6 +47,19 @@ class Runtime:
         self._keep.append(bsk)
         return int(self.lib.concrete_b200_context_add_bsk(self.ctx, bsk.ctypes.data, bsk.size))
 
+    def add_seeded_ksk(self, bodies: np.ndarray, full_len: int, seed: int) -> int:
+        """Seeded keyswitch key (bodies + u128 compression seed); masks regenerated per device."""
+        bodies = np.ascontiguousarray(bodies, dtype=np.uint64)
+        self._keep.append(bodies)
+        return int(self.lib.concrete_b200_context_add_seeded_ksk(
+            self.ctx, bodies.ctypes.data, full_len, seed & (2 ** 64 - 1), seed >> 64))
+
+    def add_seeded_bsk(self, bodies: np.ndarray, full_len: int, seed: int) -> int:
+        bodies = np.ascontiguousarray(bodies, dtype=np.uint64)
+        self._keep.append(bodies)
+        return int(self.lib.concrete_b200_context_add_seeded_bsk(
+            self.ctx, bodies.ctypes.data, full_len, seed & (2 ** 64 - 1), seed >> 64))
+
     def batched_keyswitch(self, out, ct0, level, base_log, n_in, n_out, ksk_index, cpu_named=False):
         f = self.lib.memref_batched_keyswitch_lwe_u64 if cpu_named else self.lib.memref_batched_keyswitch_lwe_cuda_u64
         f(*_m2(out), *_m2(ct0), level, base_log, n_in, n_out, ksk_index, self.ctx)

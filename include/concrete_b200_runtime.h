@@ -26,6 +26,15 @@ void *concrete_b200_context_create(void);
 void concrete_b200_context_destroy(void *ctx);
 uint64_t concrete_b200_context_add_ksk(void *ctx, const uint64_t *data, uint64_t len_words);
 uint64_t concrete_b200_context_add_bsk(void *ctx, const uint64_t *data, uint64_t len_words);
+/* seeded (compressed) keys: bodies + 128-bit compression seed; `full_len_words` is the word count
+ * of the decompressed key.  The masks are regenerated on every device (concrete_b200.h, seeded
+ * keys) when get_{ksk,bsk}_gpu first needs the key there. */
+uint64_t concrete_b200_context_add_seeded_ksk(void *ctx, const uint64_t *bodies,
+                                              uint64_t full_len_words, uint64_t seed_lo,
+                                              uint64_t seed_hi);
+uint64_t concrete_b200_context_add_seeded_bsk(void *ctx, const uint64_t *bodies,
+                                              uint64_t full_len_words, uint64_t seed_lo,
+                                              uint64_t seed_hi);
 void concrete_b200_context_set_num_gpus(void *ctx, int n); /* same knob as env SDFG_NUM_GPUS */
 void concrete_b200_context_set_device_base(void *ctx, int base); /* first device (LOCAL_RANK) */
 

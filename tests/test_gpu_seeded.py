@@ -91,3 +91,36 @@ def test_seeded_keys_drive_the_hot_path(engine, name, n_small, bits):
     out_full = as_u64(engine.bootstrap(d_mid, d_lut, None, d_fbsk_full, p.n, p.k, p.N, p.b, p.l))
     assert np.array_equal(out, out_full)
     assert np.array_equal(ks.decrypt_big(out, bits), table[msgs])
+
+
+def test_seeded_keys_through_the_runtime_wrappers(engine):
+    """memref_batched_* with the context holding SEEDED keys (what the keyset ships): the
+    per-device key copies are built by the device-side decompression on first use; outputs equal
+    those of a context holding the full keys, word for word."""
+    from concrete_b200.runtime import Runtime
+
+    ks = KeySet(PARAMS["TOY1024"], seed=42, compression_seeds=SEEDS)
+    p = ks.p
+    bits, num = 3, 40
+    rng = np.random.default_rng(9)
+    msgs = rng.integers(0, 1 << bits, num).astype(np.uint64)
+    table = (np.arange(1 << bits) ** 2 % (1 << bits)).astype(np.uint64)
+    lut_poly = expand_lut(table, p.N, bits)
+    cts = ks.encrypt_big(msgs, bits, seed=3)
+    outs = []
+    for seeded in (True, False):
+        rt = Runtime(num_gpus=1)
+        if seeded:
+            ki = rt.add_seeded_ksk(ks.seeded_ksk, ks.ksk.size, ks.ksk_seed)
+            bi = rt.add_seeded_bsk(ks.seeded_bsk, ks.bsk.size, ks.bsk_seed)
+        else:
+            ki, bi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk)
+        mid = np.zeros((num, p.n + 1), dtype=np.uint64)
+        out = np.zeros((num, p.big_n + 1), dtype=np.uint64)
+        rt.batched_keyswitch(mid, cts, p.l_ks, p.b_ks, p.big_n, p.n, ki)
+        rt.batched_bootstrap(out, mid, lut_poly, p.n, p.N, p.l, p.b, p.k, bi)
+        rt.close()
+        outs.append((mid, out))
+    assert np.array_equal(outs[0][0], orc.keyswitch(cts, ks.ksk, p.big_n, p.n, p.b_ks, p.l_ks))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    assert np.array_equal(ks.decrypt_big(outs[0][1], bits), table[msgs])
