@@ -296,6 +296,75 @@ poly_mul_kernel(const double *in1, const double *in2, double *out,
   }
 }
 
+// CMUX of the vertical-packing tree (WoP-PBS, wop_pbs.cu): out[p] = t0 + GGSW (x) (t1 - t0) with
+// t0 = in[2p], t1 = in[2p + 1] (GLWEs of (K+1)N words) — `cmux` of ggsw.rs applied to a whole tree
+// layer (fft64/crypto/wop_pbs/mod.rs:465-587).  One CTA per pair; the GGSW is one Fourier GGSW
+// in the generic kernel's layout (bsk_convert_kernel), shared by every pair of the layer; pairs
+// of lut `q` use ggsw + q * 0 (same selector bit for every lut).
+template <int K, int LOGN>
+__global__ void __launch_bounds__(PbsCfg<K, LOGN>::T, PbsCfg<K, LOGN>::MINB)
+cmux_kernel(u64 *__restrict__ out, const u64 *__restrict__ in, const double2 *__restrict__ ggsw,
+            const double2 *__restrict__ tw, u32 base_log, u32 level, u32 pairs) {
+  using C = PbsCfg<K, LOGN>;
+  constexpr int LOGM = C::LOGM, LOGP = C::LOGP, M = C::M, N = C::N, P = C::P, T = C::T;
+  constexpr int GS = K + 1;
+  extern __shared__ __align__(1024) unsigned char smem[];
+  double2 *fbuf = reinterpret_cast<double2 *>(smem);
+  const int t = threadIdx.x;
+  const u64 mask = ((u64)1 << base_log) - 1;
+  const u32 round_shift = 64 - base_log * level - 1, state_shift = 64 - base_log * level;
+  for (u32 pair = blockIdx.x; pair < pairs; pair += gridDim.x) {
+    const u64 *t0 = in + (size_t)(2 * pair) * GS * N, *t1 = t0 + (size_t)GS * N;
+    double2 oacc[GS][P];
+#pragma unroll
+    for (int c = 0; c < GS; ++c)
+#pragma unroll
+      for (int p = 0; p < P; ++p) oacc[c][p] = make_double2(0.0, 0.0);
+#pragma unroll 1
+    for (int r = 0; r < GS; ++r) {
+      u64 st_re[P], st_im[P];
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        st_re[p] = closest_representable(t1[r * N + j] - t0[r * N + j], round_shift) >> state_shift;
+        st_im[p] = closest_representable(t1[r * N + j + M] - t0[r * N + j + M], round_shift) >> state_shift;
+      }
+#pragma unroll 1
+      for (u32 m = 0; m < level; ++m) {
+        double2 x[P];
+#pragma unroll
+        for (int p = 0; p < P; ++p) {
+          x[p].x = __int2double_rn((int)(u32)decompose_one_level(st_re[p], mask, base_log));
+          x[p].y = __int2double_rn((int)(u32)decompose_one_level(st_im[p], mask, base_log));
+        }
+        cbfft::forward<LOGM, LOGP>(x, fbuf, t, tw);
+        const double2 *__restrict__ g = ggsw + (((size_t)m * GS + r) * GS) * M + t;
+#pragma unroll
+        for (int c = 0; c < GS; ++c) {
+#pragma unroll
+          for (int p = 0; p < P; ++p) {
+            const double2 w = __ldg(&g[(size_t)c * M + p * T]);
+            oacc[c][p].x = fma(x[p].x, w.x, fma(-x[p].y, w.y, oacc[c][p].x));
+            oacc[c][p].y = fma(x[p].x, w.y, fma(x[p].y, w.x, oacc[c][p].y));
+          }
+        }
+      }
+    }
+    u64 *o = out + (size_t)pair * GS * N;
+#pragma unroll
+    for (int c = 0; c < GS; ++c) {
+      cbfft::inverse<LOGM, LOGP>(oacc[c], fbuf, t, tw);
+#pragma unroll
+      for (int p = 0; p < P; ++p) {
+        const int j = t + p * T;
+        o[c * N + j] = t0[c * N + j] + from_torus(oacc[c][p].x);
+        o[c * N + j + M] = t0[c * N + j + M] + from_torus(oacc[c][p].y);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // Host-side dispatch
 // ------------------------------------------------------------------------------------------
@@ -312,6 +381,7 @@ struct Variant {
   bool cl_fits;
   void (*convert)(double2 *, const double2 *, size_t);
   void (*polymul)(const double *, const double *, double *, const double2 *, u32);
+  void (*cmux)(u64 *, const u64 *, const double2 *, const double2 *, u32, u32, u32);
   int T;
   size_t fbuf_bytes, acc_bytes;
   bool acc_global;
@@ -333,6 +403,7 @@ template <int K, int LOGN> Variant make_variant() {
   v.cl_fits = GrpCfg<K, LOGN>::CL_FITS;
   v.convert = bsk_convert_kernel<K, LOGN>;
   v.polymul = poly_mul_kernel<K, LOGN>;
+  v.cmux = cmux_kernel<K, LOGN>;
   v.T = C::T;
   v.fbuf_bytes = C::FBUF_BYTES;
   v.acc_bytes = C::ACC_BYTES;
@@ -628,6 +699,42 @@ void cb_bsk_convert(cudaStream_t stream, int gpu, void *dest, const void *src_ho
                                 (int)v.fbuf_bytes));
   const u32 grid = (u32)std::min<size_t>(polys, (size_t)sms * 8);
   v.convert<<<grid, v.T, v.fbuf_bytes, stream>>>(reinterpret_cast<double2 *>(dest), tw, polys);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+// One Fourier GGSW list in the GENERIC kernel's layout (what cmux_kernel reads), in place on the
+// device, whatever family serves (k, N) for the PBS.
+void cb_ggsw_convert_generic(cudaStream_t stream, int gpu, void *data, size_t polys, u32 k, u32 N) {
+  Variant v;
+  if (!get_variant(k, N, v))
+    CB_PANIC("Cuda error (convert GGSW): unsupported (glwe_dimension=%u, polynomial_size=%u)", k, N);
+  if (polys == 0) return;
+  const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
+  int sms = 0;
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  CB_CHECK(cudaFuncSetAttribute(v.convert, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.fbuf_bytes));
+  const u32 grid = (u32)std::min<size_t>(polys, (size_t)sms * 8);
+  v.convert<<<grid, v.T, v.fbuf_bytes, stream>>>(reinterpret_cast<double2 *>(data), tw, polys);
+  CB_CHECK(cudaGetLastError());
+  CB_LAUNCHED();
+}
+
+// out[p] = in[2p] + ggsw (x) (in[2p+1] - in[2p]) for p < pairs (GLWEs of (k+1)N words)
+void cb_cmux_launch(cudaStream_t stream, int gpu, u64 *out, const u64 *in, const double2 *ggsw,
+                    u32 k, u32 N, u32 base_log, u32 level, u32 pairs) {
+  Variant v;
+  if (!get_variant(k, N, v))
+    CB_PANIC("Cuda error (cmux): unsupported (glwe_dimension=%u, polynomial_size=%u)", k, N);
+  if (pairs == 0) return;
+  const double2 *tw = get_twiddles(gpu, (int)std::lround(std::log2((double)N)) - 1);
+  int sms = 0;
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));
+  CB_CHECK(cudaFuncSetAttribute(v.cmux, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)v.fbuf_bytes));
+  const u32 grid = std::min<u32>(pairs, (u32)sms * 4);
+  v.cmux<<<grid, v.T, v.fbuf_bytes, stream>>>(out, in, ggsw, tw, base_log, level, pairs);
   CB_CHECK(cudaGetLastError());
   CB_LAUNCHED();
 }

@@ -171,6 +171,37 @@ class Engine:
             p.big_n, p.n, p.b_ks, p.l_ks, p.k, p.N, p.b, p.l, num)
         return out
 
+    # ------------------------------------------------------------------ WoP-PBS
+    def extract_bits(self, cts: torch.Tensor, nbits, fbsk, ksk, p) -> torch.Tensor:
+        """`p`: an object with n, k, N, bsk_b, bsk_l, ks_b, ks_l (tests/wop_harness.WopParams)."""
+        nb = (C.c_uint32 * len(nbits))(*nbits)
+        out = torch.zeros((sum(nbits), p.n + 1), dtype=torch.int64, device=self.device)
+        self.lib.cuda_extract_bits_lwe_ciphertext_vector_64(
+            self.stream, self.gpu, out.data_ptr(), cts.data_ptr(), nb, len(nbits), fbsk.data_ptr(),
+            ksk.data_ptr(), p.n, p.k, p.N, p.bsk_l, p.bsk_b, p.ks_l, p.ks_b)
+        return out
+
+    def circuit_bootstrap_vertical_packing(self, bits: torch.Tensor, luts: torch.Tensor, fbsk, pfpksk,
+                                           p) -> torch.Tensor:
+        nbits, lut_count, lut_size = int(bits.shape[0]), int(luts.shape[0]), int(luts.shape[1])
+        out = torch.empty((lut_count, p.k * p.N + 1), dtype=torch.int64, device=self.device)
+        self.lib.cuda_circuit_bootstrap_vertical_packing_lwe_ciphertext_vector_64(
+            self.stream, self.gpu, out.data_ptr(), bits.data_ptr(), luts.data_ptr(), fbsk.data_ptr(),
+            pfpksk.data_ptr(), nbits, lut_count, lut_size, p.n, p.k, p.N, p.bsk_l, p.bsk_b, p.pks_l,
+            p.pks_b, p.cbs_l, p.cbs_b)
+        return out
+
+    def wop_pbs_crt(self, cts: torch.Tensor, lut_ct: torch.Tensor, moduli, fbsk, ksk, pfpksk,
+                    p) -> torch.Tensor:
+        """memref_wop_pbs_crt_buffer (wrappers.cpp:855-997) with device-resident operands."""
+        crt = (C.c_uint64 * len(moduli))(*moduli)
+        out = torch.empty_like(cts)
+        self.lib.cuda_wop_pbs_crt_lwe_ciphertext_vector_64(
+            self.stream, self.gpu, out.data_ptr(), cts.data_ptr(), lut_ct.data_ptr(), crt,
+            len(moduli), fbsk.data_ptr(), ksk.data_ptr(), pfpksk.data_ptr(), p.n, p.k, p.N, p.bsk_l,
+            p.bsk_b, p.ks_l, p.ks_b, p.pks_l, p.pks_b, p.cbs_l, p.cbs_b)
+        return out
+
     def fourier_polynomial_mul(self, a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
         total, N = a.shape
         out = torch.empty_like(a)

@@ -59,6 +59,13 @@ SIGNATURES = {
     "cuda_decompress_seeded_lwe_keyswitch_key_64": (None, [vp, u32, vp, vp, u32, u32, u32, u64, u64]),
     "cuda_convert_seeded_lwe_programmable_bootstrap_key_64": (
         None, [vp, u32, vp, vp, u32, u32, u32, u32, u64, u64]),
+    "cuda_extract_bits_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, u32, vp, vp, u32, u32, u32, u32, u32, u32, u32]),
+    "cuda_circuit_bootstrap_vertical_packing_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, vp, u32, u32, u64, u32, u32, u32, u32, u32, u32, u32, u32, u32]),
+    "cuda_wop_pbs_crt_lwe_ciphertext_vector_64": (
+        None, [vp, u32, vp, vp, vp, vp, u32, vp, vp, vp, u32, u32, u32, u32, u32, u32, u32, u32, u32,
+               u32, u32]),
     "concrete_b200_version": (C.c_char_p, []),
     "concrete_b200_kernel_launches": (u64, []),
     "concrete_b200_set_pbs_plan": (None, [C.c_int]),

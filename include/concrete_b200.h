@@ -214,6 +214,44 @@ void cuda_convert_seeded_lwe_programmable_bootstrap_key_64(
     uint32_t glwe_dim, uint32_t level_count, uint32_t polynomial_size, uint64_t seed_lo,
     uint64_t seed_hi);
 
+/* ---- WoP-PBS on the device ---------------------------------------------------
+ * The reference runs this path on the CPU only (memref_wop_pbs_crt_buffer,
+ * compilers/concrete-compiler/compiler/lib/Runtime/wrappers.cpp:855-997, over
+ * concrete_cpu_extract_bit_lwe_ciphertext_u64 and
+ * concrete_cpu_circuit_bootstrap_boolean_vertical_packing_lwe_ciphertext_u64,
+ * backends/concrete-cpu/implementation/src/c_api/wop_pbs.rs:103-412).  Same arithmetic, same
+ * argument meaning; all array arguments are DEVICE pointers except the small parameter arrays
+ * (`number_of_bits`, `crt_decomposition`: host).  `fourier_bsk` is the key produced by
+ * cuda_convert_lwe_programmable_bootstrap_key_64, `ksk` the raw big->small keyswitching key,
+ * `pfpksk` the (k+1) private functional packing keyswitching keys of the circuit bootstrap, raw
+ * tfhe-rs layout [k+1][kN+1][level][(k+1)N].
+ *   extract_bits: block i yields number_of_bits[i] ciphertexts (MSB first) with
+ *     delta_log = 64 - number_of_bits[i]; the bit list is laid out as the runtime expects, the LAST
+ *     block first (wrappers.cpp:903-909); the input is used as is (the caller applies the rounding
+ *     trick of wrappers.cpp:928-931 if it wants it — cuda_wop_pbs_crt_... does);
+ *   circuit_bootstrap_vertical_packing: `bits_in` [number_of_bits][n+1], `luts`
+ *     [lut_count][2^number_of_bits], out [lut_count][kN+1];
+ *   wop_pbs_crt: the whole memref_wop_pbs_crt_buffer, in/out [blocks][kN+1],
+ *     lut_ct [blocks][2^total_bits]. */
+void cuda_extract_bits_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *bits_out, const void *lwe_array_in,
+    const uint32_t *number_of_bits, uint32_t blocks, const void *fourier_bsk, const void *ksk,
+    uint32_t lwe_small_dim, uint32_t glwe_dim, uint32_t polynomial_size, uint32_t bsk_level,
+    uint32_t bsk_base_log, uint32_t ksk_level, uint32_t ksk_base_log);
+void cuda_circuit_bootstrap_vertical_packing_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, const void *bits_in, const void *luts,
+    const void *fourier_bsk, const void *pfpksk, uint32_t number_of_bits, uint32_t lut_count,
+    uint64_t lut_size, uint32_t lwe_small_dim, uint32_t glwe_dim, uint32_t polynomial_size,
+    uint32_t bsk_level, uint32_t bsk_base_log, uint32_t pksk_level, uint32_t pksk_base_log,
+    uint32_t cbs_level, uint32_t cbs_base_log);
+void cuda_wop_pbs_crt_lwe_ciphertext_vector_64(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, const void *lwe_array_in,
+    const void *lut_ct, const uint64_t *crt_decomposition, uint32_t blocks, const void *fourier_bsk,
+    const void *ksk, const void *pfpksk, uint32_t lwe_small_dim, uint32_t glwe_dim,
+    uint32_t polynomial_size, uint32_t bsk_level, uint32_t bsk_base_log, uint32_t ksk_level,
+    uint32_t ksk_base_log, uint32_t pksk_level, uint32_t pksk_base_log, uint32_t cbs_level,
+    uint32_t cbs_base_log);
+
 uint64_t concrete_b200_kernel_launches(void);
 /* TEST hooks (not in the reference): pin the kernel family so that the tests keep every kernel
  * covered.  PBS: 0 automatic, 1 first generic kernel, 2 group kernel, 3 cluster kernel, 4 v4

@@ -56,9 +56,9 @@ def lib(native: bool = False):
     if _LIB_NATIVE is not None and native:
         return _LIB_NATIVE
     path = os.path.join(_HERE, _native_name() if native else "liboracle.so")
-    src = os.path.join(_HERE, "tfhe_oracle.cpp")
-    if not os.path.exists(path) or (
-        os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(path)
+    srcs = [os.path.join(_HERE, f) for f in ("tfhe_oracle.cpp", "csprng_oracle.cpp", "wop_oracle.inl")]
+    if not os.path.exists(path) or any(
+        os.path.exists(src) and os.path.getmtime(src) > os.path.getmtime(path) for src in srcs
     ):
         build(native)
     l = C.CDLL(path)
@@ -358,4 +358,54 @@ def decompress_seeded_ksk(seeded, n_in, n_out, level, seed: int) -> np.ndarray:
     lo, hi = _seed_halves(seed)
     lib().orc_decompress_seeded_ksk(_p(out), _p(np.ascontiguousarray(seeded)), n_in, n_out, level,
                                     lo, hi)
+    return out
+
+
+# ---------------------------------------------------------------- WoP-PBS (wop_oracle.inl)
+def gen_cbs_pfpksk_list(lwe_key_in, glwe_key, k, N, base_log, level, sigma, seed) -> np.ndarray:
+    """(k+1) private functional packing keyswitch keys [k+1][n_in+1][level][(k+1)N]."""
+    n_in = len(lwe_key_in)
+    out = np.empty((k + 1) * (n_in + 1) * level * (k + 1) * N, dtype=np.uint64)
+    lib().orc_gen_cbs_pfpksk_list(_p(out), _p(lwe_key_in), n_in, _p(glwe_key), k, C.c_size_t(N),
+                                  base_log, level, C.c_double(sigma), C.c_uint64(seed))
+    return out
+
+
+def extract_bits(lwe_in, fbsk, ksk, n_small, k, N, bsk_b, bsk_l, ks_b, ks_l, delta_log, nbits):
+    out = np.empty((nbits, n_small + 1), dtype=np.uint64)
+    lib().orc_extract_bits(_p(out), _p(np.ascontiguousarray(lwe_in)), _p(fbsk, np.complex128), _p(ksk),
+                           n_small, k, C.c_size_t(N), bsk_b, bsk_l, ks_b, ks_l, delta_log, nbits)
+    return out
+
+
+def circuit_bootstrap_boolean(lwe_in, fbsk, pfpksk, n_small, k, N, bsk_b, bsk_l, pks_b, pks_l,
+                              cbs_b, cbs_l, delta_log=63):
+    out = np.empty(cbs_l * (k + 1) * (k + 1) * N, dtype=np.uint64)
+    lib().orc_circuit_bootstrap_boolean(_p(out), _p(np.ascontiguousarray(lwe_in)),
+                                        _p(fbsk, np.complex128), _p(pfpksk), n_small, k,
+                                        C.c_size_t(N), bsk_b, bsk_l, pks_b, pks_l, cbs_b, cbs_l,
+                                        delta_log)
+    return out
+
+
+def cbs_vertical_packing(bits_in, luts, fbsk, pfpksk, n_small, k, N, bsk_b, bsk_l, pks_b, pks_l,
+                         cbs_b, cbs_l):
+    nbits = bits_in.shape[0]
+    lut_count, lut_size = luts.shape
+    out = np.empty((lut_count, k * N + 1), dtype=np.uint64)
+    lib().orc_cbs_vertical_packing(_p(out), _p(np.ascontiguousarray(bits_in)),
+                                   _p(np.ascontiguousarray(luts)), _p(fbsk, np.complex128),
+                                   _p(pfpksk), n_small, k, C.c_size_t(N), bsk_b, bsk_l, pks_b, pks_l,
+                                   cbs_b, cbs_l, nbits, C.c_size_t(lut_count), C.c_size_t(lut_size))
+    return out
+
+
+def wop_pbs_crt(cts_in, lut_ct, crt_decomp, fbsk, ksk, pfpksk, n_small, k, N, bsk_b, bsk_l, ks_b,
+                ks_l, pks_b, pks_l, cbs_b, cbs_l):
+    blocks = cts_in.shape[0]
+    out = np.empty_like(cts_in)
+    lib().orc_wop_pbs_crt(_p(out), _p(np.ascontiguousarray(cts_in)), _p(np.ascontiguousarray(lut_ct)),
+                          _p(np.ascontiguousarray(crt_decomp, dtype=np.uint64)), blocks,
+                          _p(fbsk, np.complex128), _p(ksk), _p(pfpksk), n_small, k, C.c_size_t(N),
+                          bsk_b, bsk_l, ks_b, ks_l, pks_b, pks_l, cbs_b, cbs_l)
     return out

@@ -696,3 +696,5 @@ void orc_gen_bsk_masks(u64 *bsk, const u64 *lwe_key /*n*/, const u64 *glwe_key /
 }
 
 } // extern "C"
+
+#include "wop_oracle.inl"
