@@ -79,6 +79,7 @@ typedef struct RuntimeContext {
     }
     bsk_gpu.resize(num_devices);
     ksk_gpu.resize(num_devices);
+    pksk_gpu.resize(num_devices);
   }
 
   virtual ~RuntimeContext() {
@@ -86,6 +87,8 @@ typedef struct RuntimeContext {
       for (auto k : bsk_gpu[i])
         if (k != nullptr) cuda_drop(k, i);
       for (auto k : ksk_gpu[i])
+        if (k != nullptr) cuda_drop(k, i);
+      for (auto k : pksk_gpu[i])
         if (k != nullptr) cuda_drop(k, i);
       GpuSlot &s = *slots[i];
       if (s.stream) {
@@ -130,6 +133,26 @@ typedef struct RuntimeContext {
     host_bsks[id].seed_lo = seed_lo;
     host_bsks[id].seed_hi = seed_hi;
     return id;
+  }
+
+  // packing keyswitch keys of the circuit bootstrap (context.h fp_keyswitch_key_buffer)
+  size_t add_packing_keyswitch_key(const uint64_t *data, size_t len) {
+    host_pksks.push_back({data, len});
+    for (auto &v : pksk_gpu) v.push_back(nullptr);
+    return host_pksks.size() - 1;
+  }
+  // raw upload, cached per device like get_ksk_gpu
+  void *get_pksk_gpu(uint32_t gpu_idx, void *stream, uint32_t pksk_idx) {
+    if (pksk_gpu[gpu_idx][pksk_idx] != nullptr) return pksk_gpu[gpu_idx][pksk_idx];
+    const std::lock_guard<std::mutex> guard(*ksk_gpu_mutex[gpu_idx]);
+    if (pksk_gpu[gpu_idx][pksk_idx] != nullptr) return pksk_gpu[gpu_idx][pksk_idx];
+    const HostKeyswitchKey &key = host_pksks[pksk_idx];
+    void *tmp = cuda_malloc_async(sizeof(uint64_t) * key.len, stream, gpu_idx);
+    cuda_memcpy_async_to_gpu(tmp, const_cast<uint64_t *>(key.data), sizeof(uint64_t) * key.len,
+                             stream, gpu_idx);
+    cuda_synchronize_stream(stream, gpu_idx);
+    pksk_gpu[gpu_idx][pksk_idx] = tmp;
+    return tmp;
   }
 
   virtual const uint64_t *keyswitch_key_buffer(size_t keyId) { return host_ksks[keyId].data; }
@@ -190,6 +213,8 @@ typedef struct RuntimeContext {
 private:
   std::vector<HostKeyswitchKey> host_ksks;
   std::vector<HostBootstrapKey> host_bsks;
+  std::vector<HostKeyswitchKey> host_pksks;
+  std::vector<std::vector<void *>> pksk_gpu;
   std::vector<std::unique_ptr<std::mutex>> bsk_gpu_mutex;
   std::vector<std::vector<void *>> bsk_gpu;
   std::vector<std::unique_ptr<std::mutex>> ksk_gpu_mutex;

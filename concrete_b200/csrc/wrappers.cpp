@@ -446,4 +446,61 @@ void memref_batched_keyswitch_bootstrap_lwe_cuda_u64(
   });
 }
 
+uint64_t concrete_b200_context_add_pksk(void *ctx, const uint64_t *data, uint64_t len) {
+  return static_cast<RuntimeContext *>(ctx)->add_packing_keyswitch_key(data, len);
+}
+
+// WoP-PBS over CRT blocks, HOST memrefs — same prototype and argument meaning as the reference's
+// CPU-only wrapper (compilers/concrete-compiler/compiler/lib/Runtime/wrappers.cpp:855-997); the
+// whole chain (bit extraction, circuit bootstrap, vertical packing) runs on the first device of
+// the context, operands go up once, only the `B` output blocks come back.
+void memref_wop_pbs_crt_buffer(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size_0,
+    uint64_t out_size_1, uint64_t out_stride_0, uint64_t out_stride_1, uint64_t *in_allocated,
+    uint64_t *in_aligned, uint64_t in_offset, uint64_t in_size_0, uint64_t in_size_1,
+    uint64_t in_stride_0, uint64_t in_stride_1, uint64_t *lut_ct_allocated,
+    uint64_t *lut_ct_aligned, uint64_t lut_ct_offset, uint64_t lut_ct_size0, uint64_t lut_ct_size1,
+    uint64_t lut_ct_stride0, uint64_t lut_ct_stride1, uint64_t *crt_decomp_allocated,
+    uint64_t *crt_decomp_aligned, uint64_t crt_decomp_offset, uint64_t crt_decomp_size,
+    uint64_t crt_decomp_stride, uint32_t lwe_small_dim, uint32_t cbs_level_count,
+    uint32_t cbs_base_log, uint32_t ksk_level_count, uint32_t ksk_base_log,
+    uint32_t bsk_level_count, uint32_t bsk_base_log, uint32_t fpksk_level_count,
+    uint32_t fpksk_base_log, uint32_t polynomial_size, uint32_t ksk_index, uint32_t bsk_index,
+    uint32_t pksk_index, RuntimeContext *context) {
+  (void)out_allocated; (void)in_allocated; (void)lut_ct_allocated; (void)crt_decomp_allocated;
+  (void)out_stride_0; (void)in_stride_1; (void)lut_ct_stride0; (void)lut_ct_stride1;
+  (void)crt_decomp_stride;
+  assert(out_stride_1 == 1);
+  assert(in_stride_0 == in_size_1);
+  assert(out_size_0 == in_size_0 && out_size_0 == crt_decomp_size);
+  assert(out_size_1 == in_size_1);
+  (void)out_stride_1; (void)in_stride_0; (void)in_size_0;
+  const uint64_t big_size = in_size_1, big_dim = big_size - 1;
+  assert(big_dim % polynomial_size == 0);
+  const uint32_t glwe_dim = (uint32_t)(big_dim / polynomial_size);
+  const uint32_t blocks = (uint32_t)crt_decomp_size;
+  const uint64_t *crt = crt_decomp_aligned + crt_decomp_offset;
+  assert(lut_ct_size0 == blocks);
+  const uint32_t gpu = (uint32_t)context->device_base;
+  GpuSlot &s = context->slot(gpu);
+  const std::lock_guard<std::mutex> guard(s.mutex);
+  void *ksk = context->get_ksk_gpu(ksk_level_count, (uint32_t)big_dim, lwe_small_dim, gpu, s.stream,
+                                   ksk_index);
+  void *fbsk = context->get_bsk_gpu(lwe_small_dim, polynomial_size, bsk_level_count, glwe_dim, gpu,
+                                    s.stream, bsk_index);
+  void *pksk = context->get_pksk_gpu(gpu, s.stream, pksk_index);
+  const uint64_t ct_bytes = (uint64_t)blocks * big_size * 8, lut_bytes = lut_ct_size0 * lut_ct_size1 * 8;
+  void *d_in = ensure(s.ct_in, ct_bytes, s);
+  void *d_out = ensure(s.ct_out, ct_bytes, s);
+  void *d_lut = ensure(s.lut, lut_bytes, s);
+  cuda_memcpy_async_to_gpu(d_in, in_aligned + in_offset, ct_bytes, s.stream, gpu);
+  cuda_memcpy_async_to_gpu(d_lut, lut_ct_aligned + lut_ct_offset, lut_bytes, s.stream, gpu);
+  cuda_wop_pbs_crt_lwe_ciphertext_vector_64(
+      s.stream, gpu, d_out, d_in, d_lut, crt, blocks, fbsk, ksk, pksk, lwe_small_dim, glwe_dim,
+      polynomial_size, bsk_level_count, bsk_base_log, ksk_level_count, ksk_base_log,
+      fpksk_level_count, fpksk_base_log, cbs_level_count, cbs_base_log);
+  cuda_memcpy_async_to_cpu(out_aligned + out_offset, d_out, ct_bytes, s.stream, gpu);
+  cuda_synchronize_stream(s.stream, gpu);
+}
+
 } // extern "C"

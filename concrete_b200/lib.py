@@ -81,6 +81,9 @@ SIGNATURES.update({
     "concrete_b200_context_destroy": (None, [vp]),
     "concrete_b200_context_add_ksk": (u64, [vp, vp, u64]),
     "concrete_b200_context_add_bsk": (u64, [vp, vp, u64]),
+    "concrete_b200_context_add_pksk": (u64, [vp, vp, u64]),
+    "memref_wop_pbs_crt_buffer": (None, [vp, vp, u64, u64, u64, u64, u64, vp, vp, u64, u64, u64, u64, u64,
+                                         vp, vp, u64, u64, u64, u64, u64, vp, vp, u64, u64, u64] + [u32] * 13 + [vp]),
     "concrete_b200_context_add_seeded_ksk": (u64, [vp, vp, u64, u64, u64]),
     "concrete_b200_context_add_seeded_bsk": (u64, [vp, vp, u64, u64, u64]),
     "concrete_b200_context_set_num_gpus": (None, [vp, C.c_int]),

@@ -60,6 +60,21 @@ class Runtime:
         return int(self.lib.concrete_b200_context_add_seeded_bsk(
             self.ctx, bodies.ctypes.data, full_len, seed & (2 ** 64 - 1), seed >> 64))
 
+    def add_pksk(self, pksk: np.ndarray) -> int:
+        """The (k+1) private functional packing keyswitch keys of the circuit bootstrap."""
+        pksk = np.ascontiguousarray(pksk, dtype=np.uint64)
+        self._keep.append(pksk)
+        return int(self.lib.concrete_b200_context_add_pksk(self.ctx, pksk.ctypes.data, pksk.size))
+
+    def wop_pbs_crt(self, out, cts, lut_ct, crt_decomp, p, ksk_index=0, bsk_index=0, pksk_index=0):
+        """memref_wop_pbs_crt_buffer with HOST buffers (wrappers.cpp:855-997); `p`: WopParams."""
+        crt = np.ascontiguousarray(crt_decomp, dtype=np.uint64)
+        lut_ct = np.ascontiguousarray(lut_ct, dtype=np.uint64)
+        self.lib.memref_wop_pbs_crt_buffer(
+            *_m2(out), *_m2(cts), *_m2(lut_ct), *_m1(crt), p.n, p.cbs_l, p.cbs_b, p.ks_l, p.ks_b,
+            p.bsk_l, p.bsk_b, p.pks_l, p.pks_b, p.N, ksk_index, bsk_index, pksk_index, self.ctx)
+        return out
+
     def batched_keyswitch(self, out, ct0, level, base_log, n_in, n_out, ksk_index, cpu_named=False):
         f = self.lib.memref_batched_keyswitch_lwe_u64 if cpu_named else self.lib.memref_batched_keyswitch_lwe_cuda_u64
         f(*_m2(out), *_m2(ct0), level, base_log, n_in, n_out, ksk_index, self.ctx)

@@ -113,6 +113,24 @@ void memref_batched_keyswitch_bootstrap_lwe_cuda_u64(
     uint32_t ks_base_log, uint32_t big_lwe_dim, uint32_t small_lwe_dim, uint32_t ksk_index,
     uint32_t poly_size, uint32_t level, uint32_t base_log, uint32_t glwe_dim, uint32_t bsk_index,
     cb_runtime_context *context);
+/* WoP-PBS over CRT blocks with HOST memrefs: the reference's CPU-only wrapper
+ * (compilers/concrete-compiler/compiler/lib/Runtime/wrappers.cpp:855-997), same prototype, run on
+ * the device (csrc/wop_pbs.cu); `pksk_index` selects a key registered with
+ * concrete_b200_context_add_pksk (context.h fp_keyswitch_key_buffer). */
+uint64_t concrete_b200_context_add_pksk(void *ctx, const uint64_t *data, uint64_t len_words);
+void memref_wop_pbs_crt_buffer(
+    uint64_t *out_allocated, uint64_t *out_aligned, uint64_t out_offset, uint64_t out_size_0,
+    uint64_t out_size_1, uint64_t out_stride_0, uint64_t out_stride_1, uint64_t *in_allocated,
+    uint64_t *in_aligned, uint64_t in_offset, uint64_t in_size_0, uint64_t in_size_1,
+    uint64_t in_stride_0, uint64_t in_stride_1, uint64_t *lut_ct_allocated,
+    uint64_t *lut_ct_aligned, uint64_t lut_ct_offset, uint64_t lut_ct_size0, uint64_t lut_ct_size1,
+    uint64_t lut_ct_stride0, uint64_t lut_ct_stride1, uint64_t *crt_decomp_allocated,
+    uint64_t *crt_decomp_aligned, uint64_t crt_decomp_offset, uint64_t crt_decomp_size,
+    uint64_t crt_decomp_stride, uint32_t lwe_small_dim, uint32_t cbs_level_count,
+    uint32_t cbs_base_log, uint32_t ksk_level_count, uint32_t ksk_base_log,
+    uint32_t bsk_level_count, uint32_t bsk_base_log, uint32_t fpksk_level_count,
+    uint32_t fpksk_base_log, uint32_t polynomial_size, uint32_t ksk_index, uint32_t bsk_index,
+    uint32_t pksk_index, cb_runtime_context *context);
 
 #ifdef __cplusplus
 }

@@ -124,3 +124,25 @@ def test_wop_pbs_crt(engine, name, moduli):
         for out in (got, ref):
             dec = ks.decrypt_big_raw(out)
             assert [crt_decode(int(d), b) for d, b in zip(dec, moduli)] == want, (name, moduli, m)
+
+
+def test_wop_pbs_crt_through_the_runtime_wrapper(engine):
+    """memref_wop_pbs_crt_buffer with HOST memrefs and keys held by the RuntimeContext — the
+    reference's prototype (wrappers.cpp:855-884), executed on the device."""
+    from concrete_b200.runtime import Runtime
+
+    ks = wop_keys("WOP256")
+    p = ks.p
+    moduli = [7, 8, 5]
+    product = int(np.prod(moduli))
+    table = [(v * 5 + 2) % product for v in range(product)]
+    lut = encode_lut_for_crt_woppbs(table, moduli)
+    rt = Runtime(num_gpus=1)
+    ki, bi, pi = rt.add_ksk(ks.ksk), rt.add_bsk(ks.bsk), rt.add_pksk(ks.pfpksk)
+    for m in (1, 123, product - 1):
+        cts = ks.encrypt_big_raw([crt_encode(m, b, product) for b in moduli], seed=m)
+        out = np.zeros_like(cts)
+        rt.wop_pbs_crt(out, cts, lut, moduli, p, ki, bi, pi)
+        dec = ks.decrypt_big_raw(out)
+        assert [crt_decode(int(d), b) for d, b in zip(dec, moduli)] == [table[m] % b for b in moduli]
+    rt.close()
