@@ -6,8 +6,14 @@
 //   get_ksk_gpu(level, input_lwe_dim, output_lwe_dim, gpu_idx, stream, ksk_idx)   context.h:117-145
 //   get_bsk_gpu(input_lwe_dim, poly_size, level, glwe_dim, gpu_idx, stream, bsk_idx) context.h:86-115
 // with the same names, argument order and caching semantics (per (gpu, key) device copy behind a
-// mutex, stream synchronised before publication).  Building wrappers.cpp against the real header
-// instead only requires -DCONCRETE_B200_REAL_RUNTIME_CONTEXT and the reference's include path.
+// mutex, stream synchronised before publication).
+//
+// Porting note (honest scope): wrappers.cpp / sdfg.cpp also use what this shim ADDS to the class —
+// slot(), active_devices, device_base, the seeded / packing key registries — so they do not build
+// against the reference's context.h unchanged.  A maintainer either adds those members to the
+// real RuntimeContext (they are self-contained: the GpuSlot struct below plus three accessors) or
+// keeps them in a side table keyed by the context pointer.  The device-pointer C ABI
+// (include/concrete_b200.h) has no such dependency and is the drop-in boundary proper.
 //
 // What the shim adds is the per-GPU state the reference re-creates on every call
 // (wrappers.cpp:110-256: stream, index arrays, PBS scratch, device buffers): here it is created
