@@ -194,18 +194,18 @@ ks_kernel(u64 *__restrict__ out, const u64 *__restrict__ out_idx, const u64 *__r
 }
 
 } // namespace
-#include "keyswitch_imma.cuh"
+#include "keyswitch_umma.cuh"
 #include <cstdlib>
 
 namespace {
 
-// Tensor-core path (keyswitch_imma.cuh).  Chosen when the batch fills the GEMM tiles and the
+// Tensor-core path (keyswitch_umma.cuh).  Chosen when the batch fills the GEMM tiles and the
 // exactness conditions hold: digits fit s8 (|d| <= B/2 <= 64) and the s32 accumulators cannot
 // wrap (B/2 * 255 * K < 2^31).  Otherwise the IMAD kernel below runs; both are bit-exact.
 // concrete_b200_set_ks_plan(): TEST hook.  0 = automatic, 1 = integer-pipe kernel, 2 = INT8
 // tensor-core kernel whenever it is exact (also for batches below 512).
 std::atomic<int> g_ks_plan{0};
-bool ks_imma_eligible(u32 n_in, u32 base_log, u32 level, u32 num_samples) {
+bool ks_tensor_eligible(u32 n_in, u32 base_log, u32 level, u32 num_samples) {
   const int plan = g_ks_plan.load(std::memory_order_relaxed);
   if (plan == 1) return false;
   const bool forced = plan == 2;
@@ -235,54 +235,53 @@ cudaMemPool_t ks_scratch_pool() {
   return p;
 }
 
-void ks_imma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
+// tcgen05 path (keyswitch_umma.cuh): same exactness conditions, same pre-pass arithmetic, operands
+// written as tile images, GEMM on the 5th-generation tensor cores with TMEM accumulators.
+void ks_umma_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, const u64 *in,
                     const u64 *in_idx, const u64 *ksk, u32 n_in, u32 n_out, u32 base_log,
                     u32 level, u32 num_samples) {
   const u32 K = n_in * level, out_size = n_out + 1;
-  const u32 Kp = (K + imma::TK - 1) / imma::TK * imma::TK;
-  const u32 Np = (out_size * 8 + imma::TN - 1) / imma::TN * imma::TN;
-  // samples per chunk: digit scratch <= 256 MiB, whole tiles
-  u32 chunk = (u32)std::min<u64>(((u64)256 << 20) / Kp, (u64)num_samples + imma::TM - 1);
-  chunk = std::max<u32>(imma::TM, chunk / imma::TM * imma::TM);
-  unsigned char *Bt = nullptr;
-  signed char *D = nullptr;
-  // Scratch comes from a library-owned, stream-ordered pool that never returns memory to the
-  // driver: the default pool trims itself at every synchronisation (release threshold 0), and
-  // re-mapping ~230 MB per call costs milliseconds on one GPU and hundreds of milliseconds when
-  // 8 processes do it at once (measured: 8-GPU step 376 ms vs 236 ms on one GPU).
+  const u32 Kp = (K + umma::UKT - 1) / umma::UKT * umma::UKT;
+  const u32 Np = (out_size * 8 + umma::UN - 1) / umma::UN * umma::UN;
+  u32 chunk = (u32)std::min<u64>(((u64)256 << 20) / Kp, (u64)num_samples + umma::UM - 1);
+  chunk = std::max<u32>(umma::UM, chunk / umma::UM * umma::UM);
+  unsigned char *Bimg = nullptr;
+  signed char *Dimg = nullptr;
   cudaMemPool_t pool = ks_scratch_pool();
-  CB_CHECK(cudaMallocFromPoolAsync((void **)&Bt, (size_t)Np * Kp, pool, stream));
-  CB_CHECK(cudaMallocFromPoolAsync((void **)&D, (size_t)chunk * Kp, pool, stream));
+  CB_CHECK(cudaMallocFromPoolAsync((void **)&Bimg, (size_t)Np * Kp, pool, stream));
+  CB_CHECK(cudaMallocFromPoolAsync((void **)&Dimg, (size_t)chunk * Kp, pool, stream));
   {
     dim3 grid((Np / 8 + 31) / 32, Kp / 64);
-    imma::ks_planes_kernel<<<grid, 256, 0, stream>>>(Bt, ksk, K, out_size, Kp, Np / 8);
+    umma::ks_planes_img_kernel<<<grid, 256, 0, stream>>>(Bimg, ksk, K, out_size, Kp, Np / 8);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
   }
-  static bool attr_set[64] = {};
-  int dev = 0;
+  int dev = 0, sms = 148;
   CB_CHECK(cudaGetDevice(&dev));
+  CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  static bool attr_set[64] = {};
   if (!attr_set[dev & 63]) {
-    CB_CHECK(cudaFuncSetAttribute(imma::ks_imma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  imma::SMEM_BYTES));
+    CB_CHECK(cudaFuncSetAttribute(umma::ks_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  (int)umma::SMEM_BYTES));
     attr_set[dev & 63] = true;
   }
   for (u32 s0 = 0; s0 < num_samples; s0 += chunk) {
     const u32 count = std::min(chunk, num_samples - s0);
-    const u32 rows = (count + imma::TM - 1) / imma::TM * imma::TM;
-    dim3 gd(rows, std::min<u32>((n_in + 255) / 256, 8));
-    imma::ks_digits_kernel<<<gd, 256, 0, stream>>>(D, in, in_idx, n_in, base_log, level, s0,
-                                                   count, Kp);
+    const u32 rows = (count + umma::UM - 1) / umma::UM * umma::UM;
+    dim3 gd(rows, std::min<u32>((Kp / 16 + 255) / 256, 8));
+    umma::ks_digits_img_kernel<<<gd, 256, 0, stream>>>(Dimg, in, in_idx, n_in, base_log, level, s0,
+                                                       count, Kp);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
-    dim3 gg(Np / imma::TN, rows / imma::TM);
-    imma::ks_imma_kernel<<<gg, imma::NT, imma::SMEM_BYTES, stream>>>(
-        out, out_idx, in, in_idx, D, Bt, n_in, n_out, s0, count, Kp);
+    const u32 m_tiles = rows / umma::UM, n_tiles = Np / umma::UN;
+    const u32 grid = std::min<u32>((u32)sms, m_tiles * n_tiles);
+    umma::ks_umma_kernel<<<grid, umma::NT, umma::SMEM_BYTES, stream>>>(
+        out, out_idx, in, in_idx, Dimg, Bimg, n_in, n_out, s0, count, Kp, m_tiles, n_tiles);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
   }
-  CB_CHECK(cudaFreeAsync(D, stream));
-  CB_CHECK(cudaFreeAsync(Bt, stream));
+  CB_CHECK(cudaFreeAsync(Dimg, stream));
+  CB_CHECK(cudaFreeAsync(Bimg, stream));
 }
 
 } // namespace
@@ -296,8 +295,8 @@ void cb_keyswitch_launch(cudaStream_t stream, u64 *out, const u64 *out_idx, cons
              level);
   if (level > MAX_KT)
     CB_PANIC("Cuda error (keyswitch): level_count %u > %d unsupported", level, MAX_KT);
-  if (ks_imma_eligible(n_in, base_log, level, num_samples)) {
-    ks_imma_launch(stream, out, out_idx, in, in_idx, ksk, n_in, n_out, base_log, level,
+  if (ks_tensor_eligible(n_in, base_log, level, num_samples)) {
+    ks_umma_launch(stream, out, out_idx, in, in_idx, ksk, n_in, n_out, base_log, level,
                    num_samples);
     return;
   }

@@ -257,7 +257,7 @@ uint64_t concrete_b200_kernel_launches(void);
  * covered.  PBS: 0 automatic, 1 first generic kernel, 2 group kernel, 3 cluster kernel, 4 v4
  * (pbs_v4.cuh) wherever it has the shape; must be set BEFORE the bootstrapping key is converted
  * (the Fourier key layout belongs to the family).  Keyswitch: 0 automatic, 1 integer pipe, 2 INT8
- * tensor cores whenever exact. */
+ * tensor cores (tcgen05.mma kind::i8, TMEM accumulators) whenever exact. */
 void concrete_b200_set_pbs_plan(int plan);
 void concrete_b200_set_ks_plan(int plan);
 /* TUNING hook: alternative instantiations (key-ring geometry, state packing) of the N = 16384

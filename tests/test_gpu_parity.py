@@ -114,6 +114,31 @@ def test_keyswitch_decomposition_shapes(engine, n_in, n_out, b_ks, l_ks, num):
     assert np.array_equal(got, ref)
 
 
+@pytest.mark.parametrize("plan", [2])        # 2: the tcgen05 byte-plane GEMM whenever it is exact
+@pytest.mark.parametrize("n_in,n_out,b_ks,l_ks,num", [
+    (2048, 742, 3, 5, 700), (2048, 801, 4, 3, 129), (333, 15, 7, 9, 1025), (77, 130, 1, 3, 512),
+    (1000, 500, 2, 20, 300), (16, 3, 4, 2, 5), (4096, 880, 4, 4, 257), (96, 17, 4, 3, 70001)])
+def test_keyswitch_tensor_core_kernels(engine, plan, n_in, n_out, b_ks, l_ks, num):
+    """The tensor-core keyswitch kernel forced (also below its automatic batch threshold):
+    ragged edges in all three GEMM dimensions (samples not a multiple of 128, key columns not a
+    multiple of the 256-column tile, K not a multiple of the 128-byte stage), more tiles than
+    SMs (persistent loop, both accumulator buffers), one tile, > 65 535 rows.  Word for word
+    against the oracle; random "KSK" (the keyswitch is linear algebra over wrapping u64)."""
+    from concrete_b200 import as_u64
+
+    rng = np.random.default_rng(n_in + 31 * l_ks + plan)
+    ksk = rng.integers(0, 2 ** 64, size=n_in * l_ks * (n_out + 1), dtype=np.uint64)
+    cts = rng.integers(0, 2 ** 64, size=(num, n_in + 1), dtype=np.uint64)
+    ref = orc.keyswitch(cts, ksk, n_in, n_out, b_ks, l_ks)
+    engine.lib.concrete_b200_set_ks_plan(plan)
+    try:
+        got = as_u64(engine.keyswitch(engine.to_device(cts), engine.upload_ksk(ksk), n_in, n_out,
+                                      b_ks, l_ks))
+    finally:
+        engine.lib.concrete_b200_set_ks_plan(0)
+    assert np.array_equal(got, ref)
+
+
 def test_keyswitch_more_than_65535_rows(engine):
     """Small K (n_in * l_ks < 4096) and a batch above the 65 535 grid.y limit in ONE chunk of the
     INT8 tensor-core path: the digit kernel's row index must not sit on blockIdx.y."""

@@ -17,7 +17,7 @@ dump() { # <output name> <grep pattern on the mangled kernel name>
   cat $OUT/$1.summary.txt | head -3; tail -1 $OUT/$1.summary.txt
 }
 dump pbs_kernel_w32v3 'pbs_kernel_w32v3'
-dump ks_imma_kernel 'ks_imma_kernel'
+dump ks_umma_kernel 'ks_umma_kernel'
 dump pbs_kernel_v4_N8192 'pbs_kernel_v4INS_3CfgILi1ELi13ELi4ELi1ELb0.*ELb1ELi1EEE'
 dump pbs_kernel_v4_N4096 'pbs_kernel_v4INS_3CfgILi1ELi12ELi4ELi2ELb0.*ELb1ELi1EEE'
 dump pbs_kernel_v4_cluster_N16384 'pbs_kernel_v4INS_3CfgILi1ELi14ELi4ELi1ELb1ELi2ELi3ELb1ELb0EEELb1ELi2EEE'
