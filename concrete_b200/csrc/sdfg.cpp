@@ -68,6 +68,33 @@ namespace {
 struct Process;
 struct Dfg;
 
+// Device memory of the scheduler comes from a library-owned stream-ordered pool that keeps what it
+// has mapped: the default pool trims itself at every synchronisation, and re-mapping the
+// ~0.6 GB a P2048 x 16 384 evaluation needs costs tens of milliseconds per GET.
+cudaMemPool_t sdfg_pool(int gpu) {
+  static std::mutex mu;
+  static std::map<int, cudaMemPool_t> pools;
+  std::lock_guard<std::mutex> g(mu);
+  auto it = pools.find(gpu);
+  if (it != pools.end()) return it->second;
+  cudaMemPoolProps props = {};
+  props.allocType = cudaMemAllocationTypePinned;
+  props.handleTypes = cudaMemHandleTypeNone;
+  props.location.type = cudaMemLocationTypeDevice;
+  props.location.id = gpu;
+  cudaMemPool_t pool;
+  S_CHECK(cudaMemPoolCreate(&pool, &props));
+  unsigned long long keep = ~0ull;
+  S_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  pools[gpu] = pool;
+  return pool;
+}
+uint64_t *pool_alloc(uint64_t words, cudaStream_t stream, int gpu) {
+  void *p = nullptr;
+  S_CHECK(cudaMallocFromPoolAsync(&p, std::max<uint64_t>(words, 1) * 8, sdfg_pool(gpu), stream));
+  return static_cast<uint64_t *>(p);
+}
+
 // device copy of the rows [begin, begin + count) of a stream value on one GPU
 struct Shard {
   uint32_t gpu = 0;
@@ -149,6 +176,56 @@ Process *make_process(void *dfg, Kind kind, void *sin1, void *sin2, void *sout) 
 }
 
 // ---- PUT / host side -----------------------------------------------------------------------------
+// A PUT without ownership must not keep a reference to the caller's memory (the reference copies:
+// memref_copy_alloc, GPUDFG.cpp:1676,1704).  For a batch of ciphertexts that is only ever read as
+// a ciphertext operand the copy goes straight to where the rows will be consumed: the device
+// shards of the evaluation (same contiguous split), one blocking upload, no host copy at all.
+bool upload_at_put(Stream *s, const uint64_t *src, uint64_t rows, uint64_t cols, uint64_t stride0) {
+  Dfg *g = s->dfg;
+  if (!g || rows < 2 || rows * cols < (1u << 16)) return false;
+  RuntimeContext *ctx = nullptr;
+  bool used = false;
+  for (Process *p : g->procs) {
+    const bool second_is_ct = p->kind == K_ADD;
+    if (p->in[1] == s && !second_is_ct) return false; // table / scalar operand: wanted on the host
+    if (p->in[0] == s || (p->in[1] == s && second_is_ct)) used = true;
+    if ((p->in[0] == s || p->in[1] == s) && p->ctx) ctx = p->ctx;
+  }
+  if (!used) return false;
+  if (!ctx)
+    for (Process *p : g->procs)
+      if (p->ctx) ctx = p->ctx;
+  if (!ctx) return false;
+  const uint64_t G = (uint64_t)std::max(1, std::min<int>(g->num_gpus, (int)std::min<uint64_t>(rows, 64)));
+  const uint32_t base = (uint32_t)ctx->device_base;
+  uint64_t begin = 0;
+  std::vector<cudaStream_t> used_streams;
+  for (uint64_t d = 0; d < G; ++d) {
+    const uint64_t cnt = rows / G + (d < rows % G ? 1 : 0);
+    const uint32_t gpu = base + (uint32_t)d;
+    S_CHECK(cudaSetDevice((int)gpu));
+    GpuSlot &slot = ctx->slot(gpu);
+    if (!slot.h2d_stream) slot.h2d_stream = cuda_create_stream(gpu);
+    cudaStream_t h2d = (cudaStream_t)slot.h2d_stream;
+    Shard sh;
+    sh.gpu = gpu, sh.begin = begin, sh.count = cnt;
+    sh.dev = pool_alloc(cnt * cols, h2d, (int)gpu);
+    if (stride0 == cols) // contiguous rows: one linear copy (the 2-D path is row-granular)
+      S_CHECK(cudaMemcpyAsync(sh.dev, src + begin * cols, cnt * cols * 8, cudaMemcpyHostToDevice, h2d));
+    else
+      S_CHECK(cudaMemcpy2DAsync(sh.dev, cols * 8, src + begin * stride0, stride0 * 8, cols * 8, cnt,
+                                cudaMemcpyHostToDevice, h2d));
+    s->shards.push_back(sh);
+    used_streams.push_back(h2d);
+    begin += cnt;
+  }
+  for (uint64_t d = 0; d < G; ++d) { // the caller's buffer is free again when PUT returns
+    S_CHECK(cudaSetDevice((int)(base + d)));
+    S_CHECK(cudaStreamSynchronize(used_streams[d]));
+  }
+  return true;
+}
+
 void put_host(Stream *s, uint64_t *allocated, uint64_t *aligned, uint64_t offset, uint64_t size0,
               uint64_t size1, uint64_t stride0, uint64_t stride1, uint64_t ownership) {
   if (stride1 != 1 && size1 > 1) S_PANIC("strided memrefs not supported");
@@ -157,6 +234,10 @@ void put_host(Stream *s, uint64_t *allocated, uint64_t *aligned, uint64_t offset
   s->rows = size0;
   s->cols = size1;
   const uint64_t *src = aligned + offset;
+  if (!ownership && upload_at_put(s, src, size0, size1, stride0)) {
+    s->generation++;
+    return;
+  }
   if (ownership && (stride0 == size1 || size0 <= 1) && allocated == aligned && offset == 0) {
     s->host = allocated; // adopted: freed when the value is replaced (GPUDFG.cpp:1673-1685)
     s->host_owned = true;
@@ -259,7 +340,7 @@ void run_shard(const std::vector<Process *> &plan, uint32_t gpu, uint64_t begin,
   std::vector<std::pair<Stream *, bool>> uploads; // (stream, is a per-row operand) in plan order
   std::vector<uint64_t *> temporaries;
   auto alloc = [&](uint64_t words) {
-    return static_cast<uint64_t *>(cuda_malloc_async(std::max<uint64_t>(words, 1) * 8, stream, gpu));
+    return pool_alloc(words, cs, (int)gpu);
   };
   std::vector<uint64_t> staging; // expanded constants; must outlive the async copies
   staging.reserve(4 * cnt + 16);
@@ -433,9 +514,13 @@ void run_shard(const std::vector<Process *> &plan, uint32_t gpu, uint64_t begin,
     if (want) {
       if (d2h != cs) S_CHECK(cudaStreamWaitEvent(d2h, ev_done[c], 0));
       const uint64_t cols = want->cols;
-      S_CHECK(cudaMemcpy2DAsync(want_out + (begin + off) * want_stride, want_stride * 8,
-                                where[want].ptr + off * cols, cols * 8, cols * 8, n,
-                                cudaMemcpyDeviceToHost, d2h));
+      if (want_stride == cols)
+        S_CHECK(cudaMemcpyAsync(want_out + (begin + off) * cols, where[want].ptr + off * cols,
+                                n * cols * 8, cudaMemcpyDeviceToHost, d2h));
+      else
+        S_CHECK(cudaMemcpy2DAsync(want_out + (begin + off) * want_stride, want_stride * 8,
+                                  where[want].ptr + off * cols, cols * 8, cols * 8, n,
+                                  cudaMemcpyDeviceToHost, d2h));
     }
   }
   S_CHECK(cudaStreamSynchronize(d2h));
