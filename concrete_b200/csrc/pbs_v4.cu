@@ -22,9 +22,10 @@ struct V4Variant {
   size_t smem, smem_stash, convert_smem;
 };
 
-template <int K, int LOGN, int CPB, int RB, int NB, bool CLUSTER = false> V4Variant make_v4() {
-  using C1 = v4::Cfg<K, LOGN, 4, CPB, false, RB, NB, CLUSTER>;
-  using CL = v4::Cfg<K, LOGN, 4, CPB, true, RB, NB, CLUSTER>;
+template <int K, int LOGN, int CPB, int RB, int NB, bool CLUSTER = false, int LOGP = 4>
+V4Variant make_v4() {
+  using C1 = v4::Cfg<K, LOGN, LOGP, CPB, false, RB, NB, CLUSTER>;
+  using CL = v4::Cfg<K, LOGN, LOGP, CPB, true, RB, NB, CLUSTER>;
   V4Variant v;
   v.one_level = v4::pbs_kernel_v4<C1, true, 1>;
   v.multi_narrow = v4::pbs_kernel_v4<CL, true, 0>;
@@ -58,7 +59,10 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
     if (alt == 1) v.two_narrow = v4::pbs_kernel_v4<v4::Cfg<1, 14, 4, 1, true, 2, 3, true, true>, true, 2>;
     return true;
   }
-  if (k == 2 && N == 1024) { v = make_v4<2, 10, 5, 8, 2>(); return true; }  // 120 + 72 KiB
+  if (k == 2 && N == 1024) { // 8 points per thread: two warps per polynomial (72 + 144 KiB)
+    v = make_v4<2, 10, 3, 4, 4, false, 3>();
+    return true;
+  }
   return false;
 }
 
