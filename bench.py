@@ -440,6 +440,53 @@ def leg_cfg5(eng, kc, ops, steps, fp64_peak):
                          "note": "whole step (leveled adds + keyswitches included in the time)"}}
 
 
+def leg_wop16(eng, ops):
+    """configs[4], CRT variant: a 16-bit table lookup on a value held as CRT residues
+    (moduli 7, 8, 9, 11, 13) through WoP-PBS on the device — bit extraction (18 bits), circuit
+    bootstrap, vertical packing of five tables of 2^18 entries (CMUX tree of 8 layers + blind
+    rotation) — with the optimizer's 128-bit parameters for 16 bits of precision
+    (wop_pbs_last_128: k=2, N=1024, n=707).  One value per call, as the reference's
+    memref_wop_pbs_crt_buffer; `ops` calls back to back on one stream."""
+    from concrete_b200 import as_u64
+    from wop_harness import (WOP_PARAMS, WopKeySet, crt_decode, crt_encode,
+                             encode_lut_for_crt_woppbs)
+
+    p = WOP_PARAMS["WOP16"]
+    ks = WopKeySet(p)
+    moduli = [7, 8, 9, 11, 13]
+    product = int(np.prod(moduli))
+    table = ((np.arange(1 << 16, dtype=np.int64) ** 2 + 1) & 0xFFFF)
+    d_lut = eng.to_device(encode_lut_for_crt_woppbs(table, moduli))
+    d_fbsk = eng.convert_bsk(ks.bsk, p.n, p.k, p.bsk_l, p.N)
+    d_ksk = eng.upload_ksk(ks.ksk)
+    d_pfpksk = eng.to_device(ks.pfpksk)
+    rng = np.random.default_rng(1616)
+    vals = [int(v) for v in rng.integers(0, 1 << 16, ops)]
+    d_cts = [eng.to_device(ks.encrypt_big_raw([crt_encode(v, b, product) for b in moduli], seed=v))
+             for v in vals]
+    outs = [None] * ops
+    state = {"i": 0}
+
+    def step():
+        i = state["i"] % ops
+        outs[i] = eng.wop_pbs_crt(d_cts[i], d_lut, moduli, d_fbsk, d_ksk, d_pfpksk, p)
+        state["i"] += 1
+
+    ms = _events_ms(step, 3, ops)
+    state["i"] = 0
+    for _ in range(ops):
+        step()
+    ok = True
+    for v, o in zip(vals, outs):
+        dec = ks.decrypt_big_raw(as_u64(o))
+        ok &= [crt_decode(int(d), b) for d, b in zip(dec, moduli)] == [int(table[v]) % b for b in moduli]
+    return {"config": "configs[4], CRT variant: 16-bit TLU through WoP-PBS (extract 18 bits, circuit "
+                      "bootstrap, vertical packing of 5 x 2^18 entries), optimizer parameters for 16 bits",
+            "params": "WOP16 (k=2, N=1024, n=707, br 4x9, ks 6x2, cb 2x9, pp 2x16)", "crt": moduli,
+            "value": 1e3 / ms, "unit": "16-bit TLU/s (one value per call, one stream)",
+            "ms_per_op": ms, "ops_timed": ops, "warmup": 3, "verified_results": bool(ok)}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -712,6 +759,11 @@ def run_ours(args):
                                                "configs[0]: 4-bit TLU on 64 encrypted uint4, P4")
             configs["configs[4]"] = leg_cfg5(eng, kc, 4096, cs, fp64_peak)
             kc.drop("P4")
+            try:
+                configs["configs[4] CRT/WoP-PBS"] = leg_wop16(eng, 4 * cs)
+            except Exception as ex:
+                configs["configs[4] CRT/WoP-PBS"] = {"unavailable": repr(ex)[:300]}
+            torch.cuda.empty_cache()
             configs["configs[2] N=8192"] = leg_ks_pbs(eng, kc, "P7", 4096, cs, fp64_peak, rank,
                                                       "configs[2]: P7 (N=8192) x 4096")
             kc.drop("P7")

@@ -126,6 +126,34 @@ def test_wop_pbs_crt(engine, name, moduli):
             assert [crt_decode(int(d), b) for d, b in zip(dec, moduli)] == want, (name, moduli, m)
 
 
+def test_wop_pbs_crt_16_bit_parameters(engine):
+    """The optimizer's 128-bit parameter set for 16 bits of precision through WoP-PBS
+    (wop_pbs_last_128: k=2, N=1024, n=707, br 4x9, ks 6x2, cb 2x9, pp 2x16) with real noise: a
+    16-bit value as residues mod 7, 8, 9, 11, 13 (18 bits in all: CMUX tree of 8 layers over five
+    tables of 2^18 entries + blind rotation).  GPU and oracle both return every residue of LUT[v]."""
+    from concrete_b200 import as_u64
+
+    ks = wop_keys("WOP16")
+    p = ks.p
+    moduli = [7, 8, 9, 11, 13]
+    product = int(np.prod(moduli))
+    table = ((np.arange(1 << 16, dtype=np.int64) * 40503 + 7) & 0xFFFF)
+    lut = encode_lut_for_crt_woppbs(table, moduli)
+    d_fbsk, d_ksk, d_pfpksk = device_keys(engine, ks)
+    d_lut = engine.to_device(lut)
+    for trial, v in enumerate((0xBEEF, 65535, 1)):
+        cts = ks.encrypt_big_raw([crt_encode(v, b, product) for b in moduli], seed=900 + trial)
+        got = as_u64(engine.wop_pbs_crt(engine.to_device(cts), d_lut, moduli, d_fbsk, d_ksk, d_pfpksk, p))
+        want = [int(table[v]) % b for b in moduli]
+        dec = ks.decrypt_big_raw(got)
+        assert [crt_decode(int(d), b) for d, b in zip(dec, moduli)] == want
+        if trial == 0:  # the oracle at full size takes a few seconds: once
+            ref = orc.wop_pbs_crt(cts, lut, moduli, ks.fbsk, ks.ksk, ks.pfpksk, p.n, p.k, p.N, p.bsk_b,
+                                  p.bsk_l, p.ks_b, p.ks_l, p.pks_b, p.pks_l, p.cbs_b, p.cbs_l)
+            dref = ks.decrypt_big_raw(ref)
+            assert [crt_decode(int(d), b) for d, b in zip(dref, moduli)] == want
+
+
 def test_wop_pbs_crt_through_the_runtime_wrapper(engine):
     """memref_wop_pbs_crt_buffer with HOST memrefs and keys held by the RuntimeContext — the
     reference's prototype (wrappers.cpp:855-884), executed on the device."""

@@ -41,6 +41,13 @@ WOP_PARAMS = {
     # the shape of the reference's FFT_WOPBS_PARAMS (tfhe core_crypto/algorithms/test/mod.rs:350-372:
     # k = 1, N = 1024, wide bases split over many levels), small dimension cut for the oracle
     "WOP1024": WopParams("WOP1024", 64, 1, 1024, 4, 9, 1, 9, 4, 9, 6, 4),
+    # the optimizer's parameters for 16 bits of precision through WoP-PBS at 128-bit security
+    # (compilers/concrete-optimizer/v0-parameters/ref/wop_pbs_last_128, "16: # bits", row 0:
+    # k=2, N=2^10, n=707, br_l=4, br_b=9, ks_l=6, ks_b=2, cb_l=2, cb_b=9, pp_l=2, pp_b=16), noise
+    # from the 128-bit security curve like every other full-size set
+    "WOP16": WopParams("WOP16", 707, 2, 1024, 9, 4, 2, 6, 16, 2, 9, 2,
+                       sigma_lwe=2.0 ** max(-0.025696778711484593 * 707 + 2.675931372549016, -62),
+                       sigma_glwe=2.0 ** max(-0.025696778711484593 * 2048 + 2.675931372549016, -62)),
 }
 
 
@@ -90,14 +97,17 @@ def encode_lut_for_crt_woppbs(table, moduli):
     2^total_bits entries per output CRT block, indexed by the concatenated bit fields."""
     bits = crt_bits(moduli)
     product = int(np.prod(moduli))
+    table = np.asarray(table, dtype=np.int64)
     assert product >= len(table)
     size = 1 << sum(bits)
     out = np.zeros((len(moduli), size), dtype=np.uint64)
-    for idx, val in enumerate(table):
-        out_index, total = 0, 0
-        for base, nb in zip(moduli, bits):
-            out_index += (((idx % base) << nb) // base) << total
-            total += nb
-        for blk, base in enumerate(moduli):
-            out[blk, out_index] = crt_encode(int(val), base, product)
+    idx = np.arange(len(table), dtype=np.int64)
+    out_index, total = np.zeros(len(table), dtype=np.int64), 0
+    for base, nb in zip(moduli, bits):
+        out_index += (((idx % base) << nb) // base) << total
+        total += nb
+    for blk, base in enumerate(moduli):
+        # crt::encode (CRT.cpp:80-88): (value mod base) * 2^64 / base, exact in Python integers
+        enc = np.array([((int(v) % base) << 64) // base for v in range(base)], dtype=np.uint64)
+        out[blk, out_index] = enc[(table % product) % base]
     return out
