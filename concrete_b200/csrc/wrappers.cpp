@@ -431,18 +431,21 @@ void memref_batched_keyswitch_bootstrap_lwe_cuda_u64(
     void *d_in = ensure(s.ct_in, cnt * ct0_size1 * 8, s);
     void *d_mid = ensure(s.ct_mid, cnt * (uint64_t)(small_lwe_dim + 1) * 8, s);
     void *d_out = ensure(s.ct_out, cnt * out_size1 * 8, s);
-    cuda_memcpy_async_to_gpu(d_in, const_cast<uint64_t *>(ct0 + begin * ct0_size1),
-                             cnt * ct0_size1 * 8, s.stream, gpu);
     void *d_lut = upload_luts(s, tlu, 1, poly_size, glwe_dim, poly_size);
     void *d_lut_idx = ensure(s.lut_idx, cnt * 8, s);
     cuda_memset_async(d_lut_idx, 0, cnt * 8, s.stream, gpu);
     ensure_pbs(s, glwe_dim, poly_size, level, (uint32_t)cnt);
-    cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
-        s.stream, gpu, d_out, d_lut, d_lut_idx, d_in, ksk, fbsk, s.pbs_buffer, d_mid,
-        big_lwe_dim, small_lwe_dim, ks_base_log, ks_level, glwe_dim, poly_size, base_log, level,
-        (uint32_t)cnt);
-    cuda_memcpy_async_to_cpu(out + begin * out_size1, d_out, cnt * out_size1 * 8, s.stream, gpu);
-    cuda_synchronize_stream(s.stream, gpu);
+    // chunk pipeline: big ciphertexts of chunk c+1 upload while chunk c runs KS -> PBS on the device
+    // and chunk c-1 downloads; the small ciphertexts never leave the device
+    const uint64_t mid_w = (uint64_t)small_lwe_dim + 1;
+    run_pipelined(s, chunk_bounds(cnt, pbs_wave(gpu)), ct0 + begin * ct0_size1, ct0_size1, d_in,
+                  out + begin * out_size1, out_size1, d_out, [&](uint64_t off, uint64_t n) {
+                    cuda_keyswitch_bootstrap_lwe_ciphertext_vector_64(
+                        s.stream, gpu, (uint64_t *)d_out + off * out_size1, d_lut,
+                        (uint64_t *)d_lut_idx + off, (uint64_t *)d_in + off * ct0_size1, ksk, fbsk,
+                        s.pbs_buffer, (uint64_t *)d_mid + off * mid_w, big_lwe_dim, small_lwe_dim,
+                        ks_base_log, ks_level, glwe_dim, poly_size, base_log, level, (uint32_t)n);
+                  });
   });
 }
 
