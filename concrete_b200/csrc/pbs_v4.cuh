@@ -106,6 +106,11 @@ __device__ __forceinline__ u32 cluster_rank() {
   asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
   return r;
 }
+// Measured alternatives at P8 x 1024 (release/acquire: 626.8 ms): relaxed arrive / plain wait, which
+// order nothing, 591.5 ms (bit-identical results, but not a guarantee of the memory model, so not
+// used); ONE fencing thread per CTA between two extra CTA barriers (formally equivalent by
+// cumulativity) 642.1 ms: the cluster-scope fence is paid either way, and serialising it behind a
+// CTA barrier costs more than letting the 16 warps issue it in parallel.
 __device__ __forceinline__ void cluster_arrive() {
   asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 }
