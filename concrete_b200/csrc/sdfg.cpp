@@ -578,6 +578,31 @@ void evaluate(Stream *s, uint64_t *out, uint64_t out_stride) {
   for (Process *p : plan)
     if (p->ctx) ctx = p->ctx;
   const uint32_t base = ctx ? (uint32_t)ctx->device_base : 0;
+  // An input that lives on devices only (uploaded at PUT, or computed by an earlier plan) must be
+  // split exactly as this evaluation splits the batch; if it is not (the device count changed in
+  // between), bring it back to the host once and let the shards upload their rows from there.
+  for (Process *p : plan)
+    for (int i = 0; i < 2; ++i) {
+      Stream *in = p->in[i];
+      if (!in || in->host || in->shards.empty()) continue;
+      if (in->producer && std::find(plan.begin(), plan.end(), in->producer) != plan.end()) continue;
+      bool match = in->shards.size() == G;
+      uint64_t begin = 0;
+      for (uint64_t d = 0; match && d < G; ++d) {
+        const uint64_t cnt = rows / G + (d < rows % G ? 1 : 0);
+        match = find_shard(in, base + (uint32_t)d, begin, cnt) != nullptr;
+        begin += cnt;
+      }
+      if (match) continue;
+      in->host = static_cast<uint64_t *>(std::malloc(std::max<uint64_t>(1, in->rows * in->cols) * 8));
+      in->host_owned = true;
+      for (Shard &sh : in->shards) {
+        S_CHECK(cudaSetDevice((int)sh.gpu));
+        S_CHECK(cudaMemcpy(in->host + sh.begin * in->cols, sh.dev, sh.count * in->cols * 8,
+                           cudaMemcpyDeviceToHost));
+      }
+      in->drop_device();
+    }
   if (G == 1) {
     run_shard(plan, base, 0, rows, rows, out ? s : nullptr, out, out_stride);
     return;
