@@ -350,3 +350,141 @@ extern "C" void cuda_keyswitch_lwe_ciphertext_vector_64(
                       (const u64 *)ksk, lwe_dimension_in, lwe_dimension_out, base_log,
                       level_count, num_samples);
 }
+
+// ---- no-allocation variant ----------------------------------------------------------------------
+// concrete_b200_keyswitch_lwe_ciphertext_vector_64_no_alloc: the tcgen05 keyswitch above with its
+// two operand images (key byte planes + digits) in a fixed device array instead of the stream-
+// ordered pool, for callers that may not allocate (CUDA graph capture, serving loops, harnesses
+// that forbid cudaMalloc).  No counterpart in the reference.
+// Nothing on this path calls cudaMalloc*/cudaFree* or an allocating library routine.
+//
+// The array is held by every GPU that loads the library until the process exits.  72 MiB is the
+// smallest round size that holds the headline parameter set (P2048: key image 6144 x 10240 B =
+// 60 MiB, the rest is the digit image, >= 128 rows per chunk).  Every call shares it: the pre-
+// passes rewrite every byte of the region a call uses (padding rows and columns included), so
+// nothing has to start at zero, but two calls that overlap on the GPU (different streams) race.
+static __device__ __align__(256) unsigned char g_ks_static_scratch[CONCRETE_B200_KS_NO_ALLOC_SCRATCH_BYTES];
+
+namespace {
+
+// In host code `g_ks_static_scratch` is only a handle for the runtime; the device address comes
+// from cudaGetSymbolAddress, once per device, with that device current.
+int ks_static_scratch(int dev, unsigned char **ptr, char *err, size_t err_cap) {
+  static std::mutex mu;
+  static unsigned char *cached[64] = {};
+  if (dev < 0 || dev >= 64) {
+    std::snprintf(err, err_cap, "keyswitch_no_alloc: gpu_index %d out of range [0, 64)", dev);
+    return CONCRETE_B200_NO_ALLOC_BAD_ARGUMENT;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (!cached[dev]) {
+    void *p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, g_ks_static_scratch);
+    if (e != cudaSuccess || !p) {
+      std::snprintf(err, err_cap, "keyswitch_no_alloc: cudaGetSymbolAddress failed on gpu %d: %s",
+                    dev, cudaGetErrorString(e));
+      return CONCRETE_B200_NO_ALLOC_CUDA_ERROR;
+    }
+    e = cudaFuncSetAttribute(umma::ks_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)umma::SMEM_BYTES);
+    if (e != cudaSuccess) {
+      std::snprintf(err, err_cap, "keyswitch_no_alloc: cudaFuncSetAttribute failed on gpu %d: %s",
+                    dev, cudaGetErrorString(e));
+      return CONCRETE_B200_NO_ALLOC_CUDA_ERROR;
+    }
+    cached[dev] = static_cast<unsigned char *>(p);
+  }
+  *ptr = cached[dev];
+  return 0;
+}
+
+} // namespace
+
+extern "C" int concrete_b200_keyswitch_lwe_ciphertext_vector_64_no_alloc(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, void *lwe_output_indexes,
+    void *lwe_array_in, void *lwe_input_indexes, void *ksk, uint32_t lwe_dimension_in,
+    uint32_t lwe_dimension_out, uint32_t base_log, uint32_t level_count, uint32_t num_samples,
+    char *error_message, uint64_t error_capacity) {
+  char local[8];
+  char *err = error_message && error_capacity ? error_message : local;
+  const size_t cap = error_message && error_capacity ? (size_t)error_capacity : sizeof(local);
+  err[0] = 0;
+  if (num_samples == 0) return 0;
+  if (!lwe_array_out || !lwe_output_indexes || !lwe_array_in || !lwe_input_indexes || !ksk) {
+    std::snprintf(err, cap, "keyswitch_no_alloc: null device pointer argument");
+    return CONCRETE_B200_NO_ALLOC_BAD_ARGUMENT;
+  }
+  const u32 n_in = lwe_dimension_in, n_out = lwe_dimension_out, level = level_count;
+  if (n_in == 0 || base_log == 0 || level == 0 || base_log * level >= 64 || base_log > 7 ||
+      (((u64)n_in * level) << (base_log - 1)) * 255 >= ((u64)1 << 31)) {
+    std::snprintf(err, cap,
+                  "keyswitch_no_alloc: decomposition base_log=%u level=%u over n_in=%u is outside "
+                  "the exact INT8 range of the tensor-core kernel (base_log <= 7 and "
+                  "n_in*level*2^(base_log-1)*255 < 2^31); use "
+                  "cuda_keyswitch_lwe_ciphertext_vector_64",
+                  base_log, level, n_in);
+    return CONCRETE_B200_NO_ALLOC_UNSUPPORTED;
+  }
+  const u64 K = (u64)n_in * level, out_size = (u64)n_out + 1;
+  const u64 Kp = (K + umma::UKT - 1) / umma::UKT * umma::UKT;
+  const u64 Np = (out_size * 8 + umma::UN - 1) / umma::UN * umma::UN;
+  const u64 key_img = (Np * Kp + 255) / 256 * 256, total = CONCRETE_B200_KS_NO_ALLOC_SCRATCH_BYTES;
+  if (key_img + (u64)umma::UM * Kp > total) {
+    std::snprintf(err, cap,
+                  "keyswitch_no_alloc: n_in=%u level=%u n_out=%u needs %llu bytes of scratch (key "
+                  "image %llu x %llu + one 128-row digit tile), the fixed array holds %llu",
+                  n_in, level, n_out, (unsigned long long)(key_img + (u64)umma::UM * Kp),
+                  (unsigned long long)Np, (unsigned long long)Kp, (unsigned long long)total);
+    return CONCRETE_B200_NO_ALLOC_TOO_LARGE;
+  }
+  cudaError_t e = cudaSetDevice((int)gpu_index);
+  if (e != cudaSuccess) {
+    std::snprintf(err, cap, "keyswitch_no_alloc: cudaSetDevice(%u): %s", gpu_index,
+                  cudaGetErrorString(e));
+    return CONCRETE_B200_NO_ALLOC_CUDA_ERROR;
+  }
+  unsigned char *scratch = nullptr;
+  if (int rc = ks_static_scratch((int)gpu_index, &scratch, err, cap)) return rc;
+  int sms = 148;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, (int)gpu_index) != cudaSuccess)
+    sms = 148;
+
+  cudaStream_t st = as_stream(stream);
+  unsigned char *Bimg = scratch;
+  signed char *Dimg = reinterpret_cast<signed char *>(scratch + key_img);
+  u32 chunk = (u32)std::min<u64>((total - key_img) / Kp, (u64)num_samples + umma::UM - 1);
+  chunk = chunk / umma::UM * umma::UM; // >= UM by the size check above
+  const u64 *in = (const u64 *)lwe_array_in, *in_idx = (const u64 *)lwe_input_indexes;
+  u64 *out = (u64 *)lwe_array_out;
+  const u64 *out_idx = (const u64 *)lwe_output_indexes;
+  auto launched = [&](const char *what) -> int {
+    cudaError_t le = cudaGetLastError();
+    if (le == cudaSuccess) {
+      CB_LAUNCHED();
+      return 0;
+    }
+    std::snprintf(err, cap, "keyswitch_no_alloc: launch of %s failed: %s", what,
+                  cudaGetErrorString(le));
+    return CONCRETE_B200_NO_ALLOC_CUDA_ERROR;
+  };
+  {
+    dim3 grid((u32)((Np / 8 + 31) / 32), (u32)(Kp / 64));
+    umma::ks_planes_img_kernel<<<grid, 256, 0, st>>>(Bimg, (const u64 *)ksk, (u32)K, (u32)out_size,
+                                                     (u32)Kp, (u32)(Np / 8));
+    if (int rc = launched("ks_planes_img_kernel")) return rc;
+  }
+  for (u32 s0 = 0; s0 < num_samples; s0 += chunk) {
+    const u32 count = std::min(chunk, num_samples - s0);
+    const u32 rows = (count + umma::UM - 1) / umma::UM * umma::UM;
+    dim3 gd(rows, std::min<u32>((u32)((Kp / 16 + 255) / 256), 8));
+    umma::ks_digits_img_kernel<<<gd, 256, 0, st>>>(Dimg, in, in_idx, n_in, base_log, level, s0,
+                                                   count, (u32)Kp);
+    if (int rc = launched("ks_digits_img_kernel")) return rc;
+    const u32 m_tiles = rows / umma::UM, n_tiles = (u32)(Np / umma::UN);
+    const u32 grid = std::min<u32>((u32)sms, m_tiles * n_tiles);
+    umma::ks_umma_kernel<<<grid, umma::NT, umma::SMEM_BYTES, st>>>(
+        out, out_idx, in, in_idx, Dimg, Bimg, n_in, n_out, s0, count, (u32)Kp, m_tiles, n_tiles);
+    if (int rc = launched("ks_umma_kernel")) return rc;
+  }
+  return 0;
+}

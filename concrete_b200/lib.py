@@ -29,6 +29,8 @@ SIGNATURES = {
     "cuda_drop_async": (None, [vp, vp, u32]),
     "cuda_get_max_shared_memory": (C.c_int, [u32]),
     "cuda_keyswitch_lwe_ciphertext_vector_64": (None, [vp, u32, vp, vp, vp, vp, vp, u32, u32, u32, u32, u32]),
+    "concrete_b200_keyswitch_lwe_ciphertext_vector_64_no_alloc": (
+        C.c_int, [vp, u32, vp, vp, vp, vp, vp, u32, u32, u32, u32, u32, C.c_char_p, u64]),
     "cuda_convert_lwe_programmable_bootstrap_key_64": (None, [vp, u32, vp, vp, u32, u32, u32, u32]),
     "scratch_cuda_programmable_bootstrap_64": (None, [vp, u32, i8pp, u32, u32, u32, u32, C.c_bool]),
     "cuda_programmable_bootstrap_lwe_ciphertext_vector_64": (

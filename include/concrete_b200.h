@@ -61,6 +61,34 @@ void cuda_keyswitch_lwe_ciphertext_vector_64(
     uint32_t lwe_dimension_out, uint32_t base_log, uint32_t level_count,
     uint32_t num_samples);
 
+/* No counterpart in the reference: added for callers
+ * that may not allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  Same arguments, same device pointers and the same bit-exact result as
+ * cuda_keyswitch_lwe_ciphertext_vector_64, computed by the tcgen05 INT8 kernel with its two
+ * operand images in a fixed `static __device__` array of
+ * CONCRETE_B200_KS_NO_ALLOC_SCRATCH_BYTES (72 MiB, held by every GPU that loads the library
+ * until exit) instead of the stream-ordered pool: no cudaMalloc / cudaFree / allocating library
+ * routine on this path.
+ *   needs   256-rounded(Np * Kp) + 128 * Kp bytes <= the array, Kp = roundup(n_in * level, 128),
+ *           Np = roundup(8 * (n_out + 1), 256)  (P2048, n_in 2048 x l 5 -> n_out 742: 61.25 MiB),
+ *           and the exact-INT8 range of that kernel: base_log <= 7,
+ *           n_in * level * 2^(base_log-1) * 255 < 2^31.
+ *   returns 0, or a CONCRETE_B200_NO_ALLOC_* code with a message in error_message (may be NULL);
+ *           nothing is launched when it returns non-zero from the argument checks.
+ *   sharing every call on a GPU uses the same array.  Each call rewrites every byte it reads, so
+ *           stale contents are harmless, but calls that overlap on the GPU (two streams) race:
+ *           order them on one stream or with events. */
+#define CONCRETE_B200_KS_NO_ALLOC_SCRATCH_BYTES (72ull << 20)
+#define CONCRETE_B200_NO_ALLOC_BAD_ARGUMENT 1
+#define CONCRETE_B200_NO_ALLOC_UNSUPPORTED 2
+#define CONCRETE_B200_NO_ALLOC_TOO_LARGE 3
+#define CONCRETE_B200_NO_ALLOC_CUDA_ERROR 4
+int concrete_b200_keyswitch_lwe_ciphertext_vector_64_no_alloc(
+    void *stream, uint32_t gpu_index, void *lwe_array_out, void *lwe_output_indexes,
+    void *lwe_array_in, void *lwe_input_indexes, void *ksk, uint32_t lwe_dimension_in,
+    uint32_t lwe_dimension_out, uint32_t base_log, uint32_t level_count,
+    uint32_t num_samples, char *error_message, uint64_t error_capacity);
+
 /* ---------------------------------------------------- programmable_bootstrap.h
  * TCB/include/programmable_bootstrap.h:21-24 ; called at RT/include/concretelang/Runtime/
  * context.h:101-105.  `src` is a HOST pointer to the standard-domain BSK
