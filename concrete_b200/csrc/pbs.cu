@@ -63,6 +63,11 @@ namespace {
 
 void cb_w32_set_const_twiddles(const double2 *host_tw) {
   CB_CHECK(cudaMemcpyToSymbol(w32::c_tw, host_tw, 32 * sizeof(double2)));
+  double rho[80], t[80], sigma[32];
+  w32::lf_tables(rho, t, sigma);
+  CB_CHECK(cudaMemcpyToSymbol(w32::c_lf_rho, rho, sizeof(rho)));
+  CB_CHECK(cudaMemcpyToSymbol(w32::c_lf_t, t, sizeof(t)));
+  CB_CHECK(cudaMemcpyToSymbol(w32::c_lf_sigma, sigma, sizeof(sigma)));
 }
 const bool g_tw_hook_installed = (g_tw_hook_logm10 = cb_w32_set_const_twiddles, true);
 

@@ -110,6 +110,80 @@ __device__ __forceinline__ void inv_pass1(double2 (&x)[32]) {
   }
 }
 
+// ---- inverse pass 1 with 6-op butterflies (Linzer-Feig scaling) ----------------------------------
+// A Gentleman-Sande butterfly (u, v) <- (u + v, (u - v) * conj(w)) is 8 FP64 instructions.  With
+// the twiddle written as c * (1 + i t) (t = tan, or s * (cot + i) when |sin| > |cos|) the real
+// factor is NOT multiplied in: every slot carries a pending real scale sigma[p] that is a
+// compile-time function of the slot, the next butterfly reads its v operand through
+// rho = sigma[v] / sigma[u] (an FMA operand, free), and the last pending scale is the multiplier
+// of the FMA that starts the torus rounding.  (u + rho v, u - rho v) are 4 FMA, the rotation by
+// (1, t) is 2 FMA: 6 instructions, 160 fewer per thread and CMUX.  Only the constant-twiddle pass
+// can do this: its rho / t / sigma are the same in every lane (constant-bank operands); in the
+// lane-dependent pass they would be 32 more values per lane and a multiply per point to resolve.
+// Tables are built on the host next to c_tw (lf_tables below), butterfly index
+// bi = 16 * (4 - s) + (u << rho) + lo in the order inv_pass1 walks them.
+__host__ __device__ constexpr int lf_bitrev(int b, int bits) {
+  int r = 0;
+  for (int i = 0; i < bits; ++i) r |= ((b >> i) & 1) << (bits - 1 - i);
+  return r;
+}
+// angle of tw[2^s + u] is pi * num / den with num = 1 + 4 bitrev_s(u), den = 2^(s+2):
+// |cos| >= |sin| iff the angle is within pi/4 of 0 or pi
+__host__ __device__ constexpr bool lf_tan_form(int s, int u) {
+  const int num = 1 + 4 * lf_bitrev(u, s), den = 1 << (s + 2);
+  return 4 * num <= den || 4 * num >= 3 * den;
+}
+__constant__ double c_lf_rho[80], c_lf_t[80], c_lf_sigma[32];
+
+__device__ __forceinline__ void inv_pass1_lf(double2 (&x)[32]) {
+#pragma unroll
+  for (int s = 4; s >= 0; --s) {
+    const int rho = 4 - s;
+#pragma unroll
+    for (int u = 0; u < (1 << s); ++u) {
+#pragma unroll
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo, q = p | (1 << rho);
+        const int bi = 16 * (4 - s) + (u << rho) + lo;
+        const double r = c_lf_rho[bi], t = c_lf_t[bi];
+        const double dr = fma(-r, x[q].x, x[p].x), di = fma(-r, x[q].y, x[p].y);
+        x[p].x = fma(r, x[q].x, x[p].x);
+        x[p].y = fma(r, x[q].y, x[p].y);
+        if (lf_tan_form(s, u)) { // c * (dr + t di, di - t dr)
+          x[q].x = fma(t, di, dr);
+          x[q].y = fma(-t, dr, di);
+        } else {                 // s * (di + t dr, t di - dr), t = cot
+          x[q].x = fma(t, dr, di);
+          x[q].y = fma(t, di, -dr);
+        }
+      }
+    }
+  }
+}
+
+// host: the tables of inv_pass1_lf, from the same angles as the twiddle table (get_twiddles)
+inline void lf_tables(double (&rho_t)[80], double (&t_t)[80], double (&sigma_t)[32]) {
+  const long double pi = 3.14159265358979323846264338327950288L;
+  long double sigma[32];
+  for (int p = 0; p < 32; ++p) sigma[p] = 1.0L;
+  for (int s = 4; s >= 0; --s) {
+    const int rho = 4 - s;
+    for (int u = 0; u < (1 << s); ++u) {
+      const long double ang = pi * (long double)(1 + 4 * lf_bitrev(u, s)) / (long double)(1 << (s + 2));
+      const long double c = cosl(ang), sn = sinl(ang);
+      const bool tan_form = lf_tan_form(s, u);
+      for (int lo = 0; lo < (1 << rho); ++lo) {
+        const int p = (u << (rho + 1)) | lo, q = p | (1 << rho);
+        const int bi = 16 * (4 - s) + (u << rho) + lo;
+        rho_t[bi] = (double)(sigma[q] / sigma[p]);
+        t_t[bi] = (double)(tan_form ? sn / c : c / sn);
+        sigma[q] = sigma[p] * (tan_form ? c : sn);
+      }
+    }
+  }
+  for (int p = 0; p < 32; ++p) sigma_t[p] = (double)sigma[p];
+}
+
 // transpose between the two register layouts through a 16 KiB buffer owned by this warp
 __device__ __forceinline__ void xchg_1to2(double2 (&x)[32], double2 *buf, int lane) {
   __syncwarp();
@@ -159,6 +233,13 @@ __device__ __forceinline__ u64 from_torus_scaled(double v) {
   const double C = 1.5 * 4503599627370496.0 * 18446744073709551616.0; // 1.5 * 2^52 * 2^64
   const double r = (v + C) - C;                                        // nearest multiple of 2^64
   return (u64)__double2ll_rn(v - r);
+}
+
+// the same for v = sigma * x with the pending scale of inv_pass1_lf as an FMA operand
+__device__ __forceinline__ u64 from_torus_scaled_lf(double x, double sigma) {
+  const double C = 1.5 * 4503599627370496.0 * 18446744073709551616.0;
+  const double r = fma(sigma, x, C) - C;
+  return (u64)__double2ll_rn(fma(sigma, x, -r));
 }
 
 // closest_representable + the single balanced digit of a one-level decomposition, from the high

@@ -28,6 +28,10 @@
 // Arithmetic is unchanged from v1/v2 (same transforms, same rounding, same digit extraction).
 #pragma once
 
+#ifndef W32_V3_LF
+#define W32_V3_LF 1 // inverse pass 1 with 6-op butterflies (pbs_w32.cuh inv_pass1_lf); 0 = 8-op
+#endif
+
 namespace w32 {
 
 constexpr int CPB3 = 6;                 // ciphertexts per CTA
@@ -533,7 +537,11 @@ __device__ __noinline__ void v3_cmux(const u32 a_hat) {
     __syncwarp();
     ld_col_all<0>(P.A, x);
   }
+#if W32_V3_LF
+  inv_pass1_lf(x);
+#else
   inv_pass1(x);
+#endif
 
   const V3Phase P = v3_phase();
   const int lane = P.lane, warp = P.warp;
@@ -551,8 +559,13 @@ __device__ __noinline__ void v3_cmux(const u32 a_hat) {
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const int p = 4 * c + e;
+#if W32_V3_LF
+      re[e] = (((u64)v[4 * e + 1] << 32) | v[4 * e + 0]) + from_torus_scaled_lf(x[p].x, c_lf_sigma[p]);
+      im[e] = (((u64)v[4 * e + 3] << 32) | v[4 * e + 2]) + from_torus_scaled_lf(x[p].y, c_lf_sigma[p]);
+#else
       re[e] = (((u64)v[4 * e + 1] << 32) | v[4 * e + 0]) + from_torus_scaled(x[p].x);
       im[e] = (((u64)v[4 * e + 3] << 32) | v[4 * e + 2]) + from_torus_scaled(x[p].y);
+#endif
       acc[lane + 32 * p] = make_ulonglong2(re[e], im[e]);
     }
     pack_pairs(v, re, im);
