@@ -24,6 +24,10 @@
 // key scaling); restates bootstrap.rs:250-368, ggsw.rs:481-602, glwe_sample_extraction.rs:90-165.
 #pragma once
 
+#ifndef V4_TW_TMEM
+#define V4_TW_TMEM 1 // twiddles of the non-first passes in tensor memory (TwT below); 0 = global
+#endif
+
 namespace v4 {
 using namespace sm100;
 
@@ -132,6 +136,72 @@ template <class C> __device__ __forceinline__ int poly_of(int grp) {
   else return grp % C::GS;
 }
 
+// ---- twiddles of the non-first passes in tensor memory -----------------------------------------
+// The first pass of a transform has compile-time twiddles (constant bank).  Every later pass needs
+// P/2 twiddles that depend on the thread (tw[2^s + b], b = the index bits above the paired one);
+// read from global memory they are an L1 miss per stage at N >= 4096 (the table is 32-64 KiB, the
+// L1 left beside 227 KiB of shared memory is not), i.e. an L2 round trip in front of every stage
+// of two passes of both transforms (ncu, P7: long scoreboard 41 % of the stalls of the inverse's
+// first pass).  With one level (no Fourier-accumulator stash) half of the tensor memory is free:
+// each thread keeps its (NPASS - 1) * P/2 twiddles there (tcgen05.ld, 12 cycles) - the v3 device.
+// Slot of the twiddle of stage rho (in-thread bit paired) and block pair h >> 1 inside a pass:
+// rho = LOGP-1 -> 0; rho = LOGP-2 -> 1; rho <= LOGP-3 -> 2^(LOGP-rho-2) + (h >> 1).
+template <class C> struct TwT {
+  static constexpr int SLOTS = C::P / 2;
+  static constexpr u32 PASS_COLS = (u32)SLOTS * 4;
+  static constexpr u32 COLS = (u32)(C::NPASS - 1) * PASS_COLS;
+  static constexpr u32 QUAD_WARPS = (C::NWARPS + 3) / 4;
+  static constexpr bool ON = V4_TW_TMEM && !C::STASH && C::NPASS > 1 && C::LOGP >= 3 && C::LOGP <= 4 &&
+                             QUAD_WARPS * (C::TM_PER_WARP + COLS) <= 512;
+  static constexpr u32 BASE = QUAD_WARPS * C::TM_PER_WARP; // first twiddle column of a quadrant
+};
+__host__ __device__ constexpr int tw_slot_base(int logp, int rho) {
+  return rho == logp - 1 ? 0 : 1 << (logp - rho - 2);
+}
+__host__ __device__ constexpr int tw_slot_count(int logp, int rho) {
+  return rho >= logp - 2 ? 1 : 1 << (logp - rho - 2);
+}
+// twiddle columns of this thread for pass `pass` (>= 1)
+template <class C> __device__ __forceinline__ u32 tw_tmem(int pass) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const u32 warp = (u32)opaque_tid() >> 5;
+  return reinterpret_cast<const Ctrl *>(smem + C::OFF_CTRL)->tmem_base + (((warp & 3u) * 32u) << 16) +
+         TwT<C>::BASE + (warp >> 2) * TwT<C>::COLS + (u32)(pass - 1) * TwT<C>::PASS_COLS;
+}
+// the CNT (1, 2 or 4) twiddles of one stage: one tcgen05.ld
+template <int CNT> __device__ __forceinline__ void tw_load(u32 taddr, double2 (&w)[4]) {
+  u32 v[16];
+  if constexpr (CNT == 1) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+                 : "r"(taddr)
+                 : "memory");
+  } else if constexpr (CNT == 2) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]),
+                   "=r"(v[6]), "=r"(v[7])
+                 : "r"(taddr)
+                 : "memory");
+  } else {
+    tmem_ld16(taddr, v);
+  }
+  tmem_wait_ld();
+#pragma unroll
+  for (int e = 0; e < CNT; ++e)
+    w[e] = make_double2(__hiloint2double((int)v[4 * e + 1], (int)v[4 * e + 0]),
+                        __hiloint2double((int)v[4 * e + 3], (int)v[4 * e + 2]));
+}
+template <class C, int RHO> __device__ __forceinline__ void tw_stage(u32 tm_pass, double2 (&w)[4]) {
+  tw_load<tw_slot_count(C::LOGP, RHO)>(tm_pass + 4u * (u32)tw_slot_base(C::LOGP, RHO), w);
+}
+// stage `rho` is only known after unrolling: dispatch on it (folds to one call)
+template <class C> __device__ __forceinline__ void tw_stage_dyn(int rho, u32 tm_pass, double2 (&w)[4]) {
+  if (rho == 0) tw_stage<C, 0>(tm_pass, w);
+  else if (rho == 1) tw_stage<C, 1>(tm_pass, w);
+  else if (rho == 2) tw_stage<C, 2>(tm_pass, w);
+  else if constexpr (C::LOGP > 3) tw_stage<C, 3>(tm_pass, w);
+}
+
 // ---- transforms: the passes of fft.cuh with an XOR-swizzled exchange ---------------------------
 template <class C> __device__ __forceinline__ int swz(int idx) {
   return idx ^ ((idx >> C::LOGP) & 7);
@@ -141,13 +211,17 @@ template <class C> __device__ __forceinline__ constexpr int pass_lo(int pass) {
 }
 
 // stages [s_begin, s_end) on in-thread data (fft.cuh fwd_stages / inv_stages with pinned loads)
-template <class C>
+template <class C, bool TWM = false>
 __device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, int s_begin,
-                                           int s_end, const double2 *__restrict__ tw) {
+                                           int s_end, const double2 *__restrict__ tw,
+                                           u32 tm_pass = 0) {
   constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
 #pragma unroll
   for (int s = s_begin; s < s_end; ++s) {
     const int beta = LOGM - 1 - s, rho = beta - lo;
+    const bool from_tmem = TWM && (lo + LOGP != LOGM);
+    double2 wt[4];
+    if (from_tmem) tw_stage_dyn<C>(rho, tm_pass, wt);
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
@@ -155,7 +229,9 @@ __device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, in
       const int idx = cbfft::elem_index<LOGP>(t, r, lo);
       const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
       const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
-      const double2 w = first_pass ? cbfft::c_twg[(1 << s) + b] : ldg_tw(&tw[(1 << s) + b]);
+      const double2 w = from_tmem    ? wt[(r >> (rho + 1)) >> 1]
+                        : first_pass ? cbfft::c_twg[(1 << s) + b]
+                                     : ldg_tw(&tw[(1 << s) + b]);
       cbfft::bfly_ct(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));
@@ -164,13 +240,16 @@ __device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, in
     }
   }
 }
-template <class C>
+template <class C, bool TWM = false>
 __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, int s_hi, int s_lo,
-                                           const double2 *__restrict__ tw) {
+                                           const double2 *__restrict__ tw, u32 tm_pass = 0) {
   constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
 #pragma unroll
   for (int s = s_hi - 1; s >= s_lo; --s) {
     const int beta = LOGM - 1 - s, rho = beta - lo;
+    const bool from_tmem = TWM && (lo + LOGP != LOGM);
+    double2 wt[4];
+    if (from_tmem) tw_stage_dyn<C>(rho, tm_pass, wt);
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
@@ -178,7 +257,9 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, in
       const int idx = cbfft::elem_index<LOGP>(t, r, lo);
       const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
       const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
-      const double2 w = first_pass ? cbfft::c_twg[(1 << s) + b] : ldg_tw(&tw[(1 << s) + b]);
+      const double2 w = from_tmem    ? wt[(r >> (rho + 1)) >> 1]
+                        : first_pass ? cbfft::c_twg[(1 << s) + b]
+                                     : ldg_tw(&tw[(1 << s) + b]);
       cbfft::bfly_gs(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));
@@ -193,7 +274,7 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, in
 // `pending` (cluster variant): the partners may still be reading this CTA's buffer (their product
 // phase); the cluster barrier they arrive at afterwards is waited for right before the first
 // exchange write, i.e. behind the register-only stages of the first pass.
-template <class C>
+template <class C, bool TWM = false>
 __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__restrict__ tw,
                                         bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -204,7 +285,7 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
     const int lo = pass_lo<C>(pass);
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
-    fwd_stages<C>(x, t, lo, s0, s1, tw);
+    fwd_stages<C, TWM>(x, t, lo, s0, s1, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u);
     if (pass + 1 < C::NPASS) {
       const int lo2 = pass_lo<C>(pass + 1);
       if constexpr (C::CL) {
@@ -221,7 +302,7 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
 }
 
 // In: x[r] = F_{t*P + r}.  Out: x[r] = M * z_{t + r*T} (unnormalised).
-template <class C>
+template <class C, bool TWM = false>
 __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__restrict__ tw,
                                         bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -232,7 +313,7 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
     const int lo = pass_lo<C>(pass);
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
-    inv_stages<C>(x, t, lo, s1, s0, tw);
+    inv_stages<C, TWM>(x, t, lo, s1, s0, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u);
     if (pass > 0) {
       const int lo2 = pass_lo<C>(pass - 1);
       if constexpr (C::CL) {
@@ -467,7 +548,7 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
     }
     // its first barrier also ends the rotated reads of ACC; for m > 0 of the cluster variant the
     // partners' reads of the previous level's parked transform end at the pending cluster barrier
-    forward<C>(x, tw, C::CL && m > 0);
+    forward<C, TwT<C>::ON>(x, tw, C::CL && m > 0);
     {
       const int tid = opaque_tid(), t = tid % T, grp = tid / T;
       double2 *buf = reinterpret_cast<double2 *>(smem + (size_t)grp * C::BUF_BYTES);
@@ -612,7 +693,7 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
   }
 
   // ---- phase C: inverse transform, torus rounding, ACC += (own copy in TMEM, home in smem)
-  inverse<C>(x, tw, C::CL);
+  inverse<C, TwT<C>::ON>(x, tw, C::CL);
   {
     const int tid = opaque_tid(), t = tid % T, grp = tid / T, warp = tid >> 5;
     ulonglong2 *acc = reinterpret_cast<ulonglong2 *>(smem + (size_t)grp * C::BUF_BYTES);
@@ -693,6 +774,45 @@ __global__ void __launch_bounds__(C::THREADS, 1) pbs_kernel_v4(const PbsArgs a) 
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   const u32 tm_own = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
                      (u32)(warp >> 2) * C::TM_PER_WARP;
+
+  if constexpr (TwT<C>::ON) { // this thread's twiddles of the non-first passes -> tensor memory
+    constexpr int LOGP = C::LOGP, LOGM = C::LOGM;
+    const u32 tm_tw = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) + TwT<C>::BASE +
+                      (u32)(warp >> 2) * TwT<C>::COLS;
+#pragma unroll
+    for (int pass = 1; pass < C::NPASS; ++pass) {
+      const int lo = pass_lo<C>(pass);
+      const int s0 = pass * LOGP, s1 = (pass == C::NPASS - 1) ? LOGM : s0 + LOGP;
+      u32 v[TwT<C>::SLOTS * 4];
+#pragma unroll
+      for (int e = 0; e < TwT<C>::SLOTS * 4; ++e) v[e] = 0;
+#pragma unroll
+      for (int s = s0; s < s1; ++s) {
+        const int rho = LOGM - 1 - s - lo;
+#pragma unroll
+        for (int kk = 0; kk < tw_slot_count(LOGP, rho); ++kk) {
+          const int slot = tw_slot_base(LOGP, rho) + kk;
+          const int b = ((t >> lo) << (LOGP - rho - 1)) | (2 * kk);
+          const double2 w = a.tw[(1 << s) + b];
+          v[4 * slot + 0] = (u32)__double2loint(w.x);
+          v[4 * slot + 1] = (u32)__double2hiint(w.x);
+          v[4 * slot + 2] = (u32)__double2loint(w.y);
+          v[4 * slot + 3] = (u32)__double2hiint(w.y);
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < TwT<C>::SLOTS * 4 / 16; ++c) {
+        u32 v16[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) v16[e] = v[16 * c + e];
+        tmem_st16(tm_tw + (u32)(pass - 1) * TwT<C>::PASS_COLS + 16 * c, v16);
+      }
+      if constexpr (TwT<C>::SLOTS * 4 % 16 != 0) { // P = 8: 16 columns per pass, handled above
+        static_assert(TwT<C>::SLOTS * 4 % 16 == 0, "twiddle columns per pass");
+      }
+    }
+    tmem_wait_st();
+  }
 
   if (tid == 0) { // prologue: the first NB blocks
     for (u32 f = 0; f < (u32)C::NB && f < total_blocks; ++f)
