@@ -22,6 +22,7 @@
 
 // pbs_v4.cu
 bool cb_pbs_v4_shape(u32 k, u32 N);
+int cb_pbs_v4_logp(u32 k, u32 N);
 void cb_pbs_v4_convert(cudaStream_t stream, int gpu, void *dest, size_t polys, u32 k, u32 N);
 void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_idx,
                       const u64 *lut_vector, const u64 *lut_idx, const u64 *lwe_in,
@@ -377,6 +378,8 @@ struct Variant {
   void (*pbs)(const PbsArgs);
   void (*pbs_grp)(const PbsArgs); // group-per-polynomial kernel (pbs_grp.cuh), if it fits
   void (*pbs_grp_w)(const PbsArgs);    // same with 64-bit decomposition states (b*l > 31)
+  void (*pbs_grp_fold)(const PbsArgs); // same two reading the v4 key layout (k = 2, N = 1024 only)
+  void (*pbs_grp_fold_w)(const PbsArgs);
   void (*pbs_grp_cl_w)(const PbsArgs);
   int grp_threads;
   size_t grp_smem_fixed;
@@ -398,6 +401,12 @@ template <int K, int LOGN> Variant make_variant() {
   v.pbs = pbs_kernel<K, LOGN>;
   v.pbs_grp = pbs_kernel_grp<K, LOGN, true>;
   v.pbs_grp_w = pbs_kernel_grp<K, LOGN, false>;
+  v.pbs_grp_fold = v.pbs_grp_fold_w = nullptr;
+  if constexpr (K == 2 && LOGN == 10) { // same key as the v4 kernel of this shape (16 points/thread)
+    static_assert(PbsCfg<K, LOGN>::LOGP == 3, "fold 1 = 8 -> 16 points per thread");
+    v.pbs_grp_fold = pbs_kernel_grp<K, LOGN, true, 1>;
+    v.pbs_grp_fold_w = pbs_kernel_grp<K, LOGN, false, 1>;
+  }
   v.pbs_grp_cl_w = pbs_kernel_grp_cluster<K, LOGN, false>;
   v.grp_threads = GrpCfg<K, LOGN>::THREADS;
   v.grp_smem_fixed = GrpCfg<K, LOGN>::SMEM_FIXED;
@@ -441,12 +450,20 @@ Family key_family(u32 k, u32 N, u32 level) {
   if (plan == PLAN_GENERIC || plan == PLAN_GRP || plan == PLAN_CLUSTER) return FAM_GENERIC;
   if (plan == PLAN_V4 && cb_pbs_v4_shape(k, N)) return FAM_V4;
   if (use_w32(k, N, level)) return FAM_W32;
-  // k = 2 (P4): measured on B200 the group kernel is ahead of v4 at every batch size (16 384
-  // samples: 243 vs 256 ms; 64 samples: 3.0 vs 5.5 ms - one warp per polynomial is a long
-  // dependent chain), so v4 stays opt-in there (plan 4)
-  if (cb_pbs_v4_shape(k, N) && k == 1) return FAM_V4;
+  // k = 2 (P4): the KEY is v4's too.  Measured on B200 (profiles/r2_p4_v4_warp_per_poly.txt): v4 with
+  // one warp per polynomial, 5 ciphertexts per CTA and its twiddles in tensor memory runs 16 384
+  // samples in 191.8 ms against 228.5 ms for the group kernel, but 64 samples in 4.7 ms against
+  // 2.7 ms (one warp per polynomial is a long dependent chain: the latency of ONE PBS).  Both read
+  // the same converted key (pbs_grp.cuh FOLD), so the batch size picks the kernel at launch.
+  if (cb_pbs_v4_shape(k, N)) return FAM_V4;
   return FAM_GENERIC;
 }
+
+// k = 2, N = 1024 under FAM_V4: batches below this run the group kernel on the v4 key (one
+// ciphertext per CTA, several CTAs per SM).  Measured on B200 (profiles/r2_p4_v4_warp_per_poly.txt):
+// 64 samples 2.9 ms (group) against 4.7 ms (v4); 739 samples 13.6 ms against 8.6 ms: the v4 kernel
+// is ahead as soon as its CTAs hold more than two ciphertexts each
+constexpr u32 V4_K2_MIN_BATCH = 2 * 148 + 1;
 
 constexpr u32 PBS_MAGIC = 0xB200CB01u;
 
@@ -504,6 +521,12 @@ void cb_pbs_scratch(cudaStream_t stream, int gpu, int8_t **buffer, u32 k, u32 N,
                                   (int)gsmem));
     CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_w, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   (int)gsmem));
+    if (v.pbs_grp_fold) {
+      CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_fold, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)gsmem));
+      CB_CHECK(cudaFuncSetAttribute(v.pbs_grp_fold_w, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)gsmem));
+    }
     CB_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, v.pbs_grp, v.grp_threads, gsmem));
     b->grp_grid_cap = occ * sms;
   }
@@ -566,7 +589,11 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
   if ((u64)(lut_count - 1) * lut_stride >= N)
     CB_PANIC("Cuda error (classical PBS): lut_count*lut_stride exceeds polynomial size");
   const Family fam = key_family(k, N, level);
-  if (fam == FAM_V4) {
+  // small batch on a v4 key that the group kernel can read (k = 2, N = 1024): see key_family
+  const bool grp_on_v4_key = fam == FAM_V4 && b->v.pbs_grp_fold && b->grp_grid_cap > 0 && n <= 2048 &&
+                             g_pbs_plan.load(std::memory_order_relaxed) == PLAN_AUTO &&
+                             cb_pbs_v4_logp(k, N) == 4 && num_samples < V4_K2_MIN_BATCH;
+  if (fam == FAM_V4 && !grp_on_v4_key) {
     cb_pbs_v4_launch(stream, gpu, lwe_out, out_idx, lut_vector, lut_idx, lwe_in, in_idx, bsk, n, k,
                      N, base_log, level, num_samples, lut_count, lut_stride);
     return;
@@ -635,7 +662,9 @@ void cb_pbs_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out_id
       !(force_cluster && b->cl_cluster_cap > 0)) {
     const size_t gsmem = v.grp_smem_fixed + (((size_t)n * 2 + 15) / 16) * 16;
     const u32 ggrid = std::min<u32>((u32)b->grp_grid_cap, num_samples);
-    (base_log * level <= 31 ? v.pbs_grp : v.pbs_grp_w)<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
+    const bool narrow = base_log * level <= 31;
+    (grp_on_v4_key ? (narrow ? v.pbs_grp_fold : v.pbs_grp_fold_w)
+                   : (narrow ? v.pbs_grp : v.pbs_grp_w))<<<ggrid, v.grp_threads, gsmem, stream>>>(a);
     CB_CHECK(cudaGetLastError());
     CB_LAUNCHED();
     return;

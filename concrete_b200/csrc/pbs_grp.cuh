@@ -47,7 +47,13 @@ template <int K, int LOGN> struct GrpCfg {
   static constexpr size_t CL_STASH_BYTES = C::ACC_GLOBAL ? (size_t)T * P * sizeof(double) : 0;
 };
 
-template <int K, int LOGN, bool CLUSTER, bool NARROW>
+// FOLD > 0: the Fourier key is in the layout of the v4 kernel with 2^FOLD times as many points per
+// thread (pbs_v4.cuh: F_q at (q mod P4) * T4 + q / P4 with P4 = P << FOLD, T4 = T >> FOLD), so that
+// ONE converted key serves both kernels and the batch size alone picks between them at launch
+// (k = 2, N = 1024: this kernel for small batches - the latency of one PBS -, v4 for large ones).
+// Thread t still owns the points q = t*P + p: they sit at ((t mod 2^FOLD) * P + p) * T4 + (t >> FOLD),
+// i.e. a warp reads 2^FOLD runs of 32 >> FOLD consecutive elements per row instead of one run of 32.
+template <int K, int LOGN, bool CLUSTER, bool NARROW, int FOLD = 0>
 __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   using st_t = typename std::conditional<NARROW, u32, u64>::type;
   namespace cg = cooperative_groups;
@@ -85,6 +91,8 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   const u32 first_sample = CLUSTER ? blockIdx.x / GS : blockIdx.x;
   const u32 sample_stride = CLUSTER ? gridDim.x / GS : gridDim.x;
   const int bar_id = CLUSTER ? 1 : 1 + grp;
+  constexpr int KT = T >> FOLD; // key row stride and this thread's offset inside a key row
+  const int koff = FOLD ? (t & ((1 << FOLD) - 1)) * P * KT + (t >> FOLD) : t;
   const u32 n = a.n, base_log = a.base_log, level = a.level;
   const st_t mask = (st_t)(((u64)1 << base_log) - 1);
   const u32 round_shift = 64 - base_log * level - 1;
@@ -179,7 +187,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           }
         }
         const double2 *__restrict__ g =
-            a.bsk + (((size_t)i * level + m) * GS * GS + grp) * M + t;
+            a.bsk + (((size_t)i * level + m) * GS * GS + grp) * M + koff;
         // ---- phase B: column grp of the external product.  The own term (r = grp) reads
         // back exactly what this thread stored, so in cluster mode it runs between the arrive
         // and the wait of the cluster barrier and covers the barrier's latency.
@@ -187,7 +195,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
 #pragma unroll
           for (int p = 0; p < P; ++p) {
-            const double2 w = __ldg(&g[(size_t)grp * GS * M + p * T]);
+            const double2 w = __ldg(&g[(size_t)grp * GS * M + p * KT]);
             const double2 f = fbuf[p * T + t];
             oacc[p].x = fma(f.x, w.x, fma(-f.y, w.y, oacc[p].x));
             oacc[p].y = fma(f.x, w.y, fma(f.y, w.x, oacc[p].y));
@@ -202,7 +210,7 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
           const double2 *fr = fsrc[r];
 #pragma unroll
           for (int p = 0; p < P; ++p) {
-            const double2 w = __ldg(&g[(size_t)r * GS * M + p * T]);
+            const double2 w = __ldg(&g[(size_t)r * GS * M + p * KT]);
             const double2 f = fr[p * T];
             oacc[p].x = fma(f.x, w.x, fma(-f.y, w.y, oacc[p].x));
             oacc[p].y = fma(f.x, w.y, fma(f.y, w.x, oacc[p].y));
@@ -245,10 +253,10 @@ __device__ __forceinline__ void pbs_grp_body(const PbsArgs &a) {
   }
 }
 
-template <int K, int LOGN, bool NARROW>
+template <int K, int LOGN, bool NARROW, int FOLD = 0>
 __global__ void __launch_bounds__(GrpCfg<K, LOGN>::THREADS, GrpCfg<K, LOGN>::MINB)
 pbs_kernel_grp(const PbsArgs a) {
-  pbs_grp_body<K, LOGN, false, NARROW>(a);
+  pbs_grp_body<K, LOGN, false, NARROW, FOLD>(a);
 }
 
 // launched with cluster dimension (k+1, 1, 1): CTA rank in the cluster = polynomial index

@@ -17,7 +17,7 @@ struct V4Variant {
   void (*two_narrow)(const PbsArgs);   // l == 2 known at compile time (P8), 32-bit states
   void (*multi_wide)(const PbsArgs);   // l >= 2, base_log * l  > 31
   void (*convert)(double2 *, const double2 *, size_t);
-  int threads, T, cpb, logm;
+  int threads, T, cpb, logm, logp;
   int cluster; // CTAs per ciphertext (k+1 in the cluster variant, else 1)
   size_t smem, smem_stash, convert_smem;
 };
@@ -37,6 +37,7 @@ V4Variant make_v4() {
   v.cpb = CPB;
   v.cluster = CLUSTER ? K + 1 : 1;
   v.logm = C1::LOGM;
+  v.logp = LOGP;
   v.smem = C1::SMEM;
   v.smem_stash = CL::SMEM;
   v.convert_smem = C1::BUF_BYTES;
@@ -57,10 +58,27 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
     v = make_v4<1, 14, 1, 2, 3, true>();
     const int alt = g_v4_alt.load();
     if (alt == 1) v.two_narrow = v4::pbs_kernel_v4<v4::Cfg<1, 14, 4, 1, true, 2, 3, true, true>, true, 2>;
+    if (alt == 2) { // 32 points per thread: 8 warps, 5 + 5 + 3 stages (two exchanges instead of three)
+      using C5 = v4::Cfg<1, 14, 5, 1, true, 4, 3, true>;
+      v.two_narrow = v4::pbs_kernel_v4<C5, true, 2>;
+      v.one_level = v.multi_narrow = v.multi_wide = nullptr;
+      v.convert = v4::bsk_convert_kernel_v4<C5>;
+      v.threads = C5::THREADS;
+      v.T = C5::T;
+      v.logp = 5;
+      v.smem = v.smem_stash = C5::SMEM;
+      v.convert_smem = C5::BUF_BYTES;
+    }
     return true;
   }
-  if (k == 2 && N == 1024) { // 8 points per thread: two warps per polynomial (72 + 144 KiB)
-    v = make_v4<2, 10, 3, 4, 4, false, 3>();
+  if (k == 2 && N == 1024) {
+    // 16 points per thread = one warp per polynomial (no named barrier inside a transform), 5
+    // ciphertexts per CTA, the whole GGSW resident in the ring (120 + 72 KiB): 191.8 ms at 16 384
+    // samples (P4) against 223.5 ms for the first configuration (8 points per thread, two warps per
+    // polynomial, 3 ciphertexts per CTA, 72 + 144 KiB), which stays behind the tuning hook.
+    // pbs.cu's group kernel reads this key layout too (FOLD = 1) and takes the small batches.
+    v = make_v4<2, 10, 5, 8, 2, false, 4>();
+    if (g_v4_alt.load() == 3) v = make_v4<2, 10, 3, 4, 4, false, 3>();
     return true;
   }
   return false;
@@ -73,6 +91,12 @@ extern "C" void concrete_b200_set_v4_alt(int alt) { g_v4_alt.store(alt); }
 bool cb_pbs_v4_shape(u32 k, u32 N) {
   return (k == 1 && (N == 1024 || N == 2048 || N == 4096 || N == 8192 || N == 16384)) ||
          (k == 2 && N == 1024);
+}
+
+// log2(points per thread) of the key layout in force (pbs.cu: which group-kernel FOLD matches it)
+int cb_pbs_v4_logp(u32 k, u32 N) {
+  V4Variant v;
+  return v4_variant(k, N, v) ? v.logp : 0;
 }
 
 int cb_pbs_v4_cpb(u32 k, u32 N) {
@@ -122,6 +146,7 @@ void cb_pbs_v4_launch(cudaStream_t stream, int gpu, u64 *lwe_out, const u64 *out
                  : (base_log * level <= 31 ? (level == 2 ? v.two_narrow : v.multi_narrow)
                                            : v.multi_wide);
   const size_t smem = level == 1 ? v.smem : v.smem_stash;
+  if (!kern) CB_PANIC("Cuda error (classical PBS, v4): no kernel for this shape in the selected variant");
   CB_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int sms = 0;
   CB_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, gpu));

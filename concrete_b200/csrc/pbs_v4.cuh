@@ -28,6 +28,19 @@
 #define V4_TW_TMEM 1 // twiddles of the non-first passes in tensor memory (TwT below); 0 = global
 #endif
 
+#ifndef V4_TW_PF
+#define V4_TW_PF 0 // 1 = global-memory twiddles fetched one stage ahead (passes without TwT).  Measured at
+                   // P8 x 1024 (profiles/r2_p8_twiddle_ab.txt): 631.9 ms against 626.4 ms just in time - off
+#endif
+#ifndef V4_PROD_PIPE
+#define V4_PROD_PIPE 1 // product phase (non-cluster): key and partner loads of row p+1 issued before the
+                       // FMAs of row p, own term first and no branch on the polynomial index; 0 = first form
+#endif
+#ifndef V4_TW_CONST
+#define V4_TW_CONST 0 // 1 = warp-uniform twiddles of a non-first pass from the constant bank.  Measured at
+                      // P8 x 1024: 625.6 ms against 626.4 ms from global memory - no effect, off
+#endif
+
 namespace v4 {
 using namespace sm100;
 
@@ -202,6 +215,30 @@ template <class C> __device__ __forceinline__ void tw_stage_dyn(int rho, u32 tm_
   else if constexpr (C::LOGP > 3) tw_stage<C, 3>(tm_pass, w);
 }
 
+// ---- twiddles of the non-first passes without TwT (two levels: the tensor memory is full) --------
+// Two alternatives to the just-in-time global load, both measured at P8 and both OFF (a negative
+// result: the twiddle latency is not what bounds the two-level kernel; the exchanges and the
+// product phase are - profiles/r2_v4cl_P8_pf1c1_ncu.txt):
+// (a) V4_TW_CONST: a pass whose in-thread bits start at lo >= 5 has block indices that depend on the
+//     WARP only: stages s < 8 index the 256-entry constant table with a warp-uniform offset
+//     (N = 16384: the second pass);
+// (b) V4_TW_PF: every other stage reads its tw_slot_count twiddles from global memory ONE STAGE
+//     AHEAD of their use (the first stage of a pass right after the exchange writes, when the
+//     points' registers are dead).
+template <class C> __host__ __device__ constexpr bool tw_is_const(int lo, int s) {
+  return V4_TW_CONST && lo + C::LOGP != C::LOGM && lo >= 5 && (2 << s) <= cbfft::CONST_TW;
+}
+template <class C>
+__device__ __forceinline__ void tw_fetch(const double2 *__restrict__ tw, int t, int lo, int s,
+                                         double2 (&w)[C::P / 4]) {
+  const int rho = C::LOGM - 1 - s - lo;
+#pragma unroll
+  for (int kk = 0; kk < tw_slot_count(C::LOGP, rho); ++kk) {
+    const int b = ((t >> lo) << (C::LOGP - rho - 1)) | (2 * kk);
+    w[kk] = tw_is_const<C>(lo, s) ? cbfft::c_twg[(1 << s) + b] : ldg_tw(&tw[(1 << s) + b]);
+  }
+}
+
 // ---- transforms: the passes of fft.cuh with an XOR-swizzled exchange ---------------------------
 template <class C> __device__ __forceinline__ int swz(int idx) {
   return idx ^ ((idx >> C::LOGP) & 7);
@@ -210,18 +247,28 @@ template <class C> __device__ __forceinline__ constexpr int pass_lo(int pass) {
   return (pass == C::NPASS - 1) ? 0 : (C::LOGM - C::LOGP * (pass + 1));
 }
 
-// stages [s_begin, s_end) on in-thread data (fft.cuh fwd_stages / inv_stages with pinned loads)
+// stage s of the pass with in-thread bits [lo, lo+LOGP) takes its twiddles from registers filled
+// one stage earlier (tw_fetch)
+template <class C, bool TWM> __host__ __device__ constexpr bool tw_piped(int lo, int s) {
+  return V4_TW_PF && lo + C::LOGP != C::LOGM && !TWM && !tw_is_const<C>(lo, s);
+}
+
+// stages [s_begin, s_end) on in-thread data (fft.cuh fwd_stages / inv_stages with pinned loads).
+// wq: the twiddles of the first stage when that stage is tw_piped (fetched by the caller).
 template <class C, bool TWM = false>
 __device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, int s_begin,
-                                           int s_end, const double2 *__restrict__ tw,
-                                           u32 tm_pass = 0) {
+                                           int s_end, const double2 *__restrict__ tw, u32 tm_pass,
+                                           double2 (&wq)[C::P / 4]) {
   constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
 #pragma unroll
   for (int s = s_begin; s < s_end; ++s) {
     const int beta = LOGM - 1 - s, rho = beta - lo;
     const bool from_tmem = TWM && (lo + LOGP != LOGM);
-    double2 wt[4];
+    const bool piped = tw_piped<C, TWM>(lo, s);
+    const bool fetch_next = s + 1 < s_end && tw_piped<C, TWM>(lo, s + 1);
+    double2 wt[4], wn[P / 4];
     if (from_tmem) tw_stage_dyn<C>(rho, tm_pass, wt);
+    if (fetch_next) tw_fetch<C>(tw, t, lo, s + 1, wn);
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
@@ -229,27 +276,36 @@ __device__ __forceinline__ void fwd_stages(double2 (&x)[C::P], int t, int lo, in
       const int idx = cbfft::elem_index<LOGP>(t, r, lo);
       const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
       const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
-      const double2 w = from_tmem    ? wt[(r >> (rho + 1)) >> 1]
-                        : first_pass ? cbfft::c_twg[(1 << s) + b]
-                                     : ldg_tw(&tw[(1 << s) + b]);
+      const double2 w = from_tmem                               ? wt[(r >> (rho + 1)) >> 1]
+                        : piped                                 ? wq[(r >> (rho + 1)) >> 1]
+                        : (first_pass || tw_is_const<C>(lo, s)) ? cbfft::c_twg[(1 << s) + b]
+                                                                : ldg_tw(&tw[(1 << s) + b]);
       cbfft::bfly_ct(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));
         cbfft::bfly_ct(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
       }
     }
+    if (fetch_next) {
+#pragma unroll
+      for (int e = 0; e < P / 4; ++e) wq[e] = wn[e];
+    }
   }
 }
 template <class C, bool TWM = false>
 __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, int s_hi, int s_lo,
-                                           const double2 *__restrict__ tw, u32 tm_pass = 0) {
+                                           const double2 *__restrict__ tw, u32 tm_pass,
+                                           double2 (&wq)[C::P / 4]) {
   constexpr int P = C::P, LOGP = C::LOGP, LOGM = C::LOGM;
 #pragma unroll
   for (int s = s_hi - 1; s >= s_lo; --s) {
     const int beta = LOGM - 1 - s, rho = beta - lo;
     const bool from_tmem = TWM && (lo + LOGP != LOGM);
-    double2 wt[4];
+    const bool piped = tw_piped<C, TWM>(lo, s);
+    const bool fetch_next = s - 1 >= s_lo && tw_piped<C, TWM>(lo, s - 1);
+    double2 wt[4], wn[P / 4];
     if (from_tmem) tw_stage_dyn<C>(rho, tm_pass, wt);
+    if (fetch_next) tw_fetch<C>(tw, t, lo, s - 1, wn);
 #pragma unroll
     for (int r = 0; r < P; ++r) {
       if (r & (1 << rho)) continue;
@@ -257,14 +313,19 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, in
       const int idx = cbfft::elem_index<LOGP>(t, r, lo);
       const bool first_pass = (lo + LOGP == LOGM) && ((1 << s) + (r >> (rho + 1)) < cbfft::CONST_TW);
       const int b = first_pass ? (r >> (rho + 1)) : (idx >> (beta + 1));
-      const double2 w = from_tmem    ? wt[(r >> (rho + 1)) >> 1]
-                        : first_pass ? cbfft::c_twg[(1 << s) + b]
-                                     : ldg_tw(&tw[(1 << s) + b]);
+      const double2 w = from_tmem                               ? wt[(r >> (rho + 1)) >> 1]
+                        : piped                                 ? wq[(r >> (rho + 1)) >> 1]
+                        : (first_pass || tw_is_const<C>(lo, s)) ? cbfft::c_twg[(1 << s) + b]
+                                                                : ldg_tw(&tw[(1 << s) + b]);
       cbfft::bfly_gs(x[r], x[r | (1 << rho)], w);
       if (rho + 1 < LOGP) {
         const int r2 = r | (1 << (rho + 1));
         cbfft::bfly_gs(x[r2], x[r2 | (1 << rho)], make_double2(-w.y, w.x));
       }
+    }
+    if (fetch_next) {
+#pragma unroll
+      for (int e = 0; e < P / 4; ++e) wq[e] = wn[e];
     }
   }
 }
@@ -278,6 +339,7 @@ template <class C, bool TWM = false>
 __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__restrict__ tw,
                                         bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
+  double2 wq[C::P / 4];
 #pragma unroll
   for (int pass = 0; pass < C::NPASS; ++pass) {
     const int tid = opaque_tid(), t = tid % C::T, grp = tid / C::T;
@@ -285,7 +347,7 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
     const int lo = pass_lo<C>(pass);
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
-    fwd_stages<C, TWM>(x, t, lo, s0, s1, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u);
+    fwd_stages<C, TWM>(x, t, lo, s0, s1, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u, wq);
     if (pass + 1 < C::NPASS) {
       const int lo2 = pass_lo<C>(pass + 1);
       if constexpr (C::CL) {
@@ -294,6 +356,8 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
+      // the points' registers are dead until the exchange reads: the next pass's first twiddles
+      if (tw_piped<C, TWM>(lo2, s1)) tw_fetch<C>(tw, t, lo2, s1, wq);
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) x[r] = buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo2))];
@@ -306,6 +370,9 @@ template <class C, bool TWM = false>
 __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__restrict__ tw,
                                         bool pending = false) {
   extern __shared__ __align__(1024) unsigned char smem[];
+  double2 wq[C::P / 4];
+  if (C::NPASS > 1 && tw_piped<C, TWM>(0, C::LOGM - 1))
+    tw_fetch<C>(tw, opaque_tid() % C::T, 0, C::LOGM - 1, wq);
 #pragma unroll
   for (int pass = C::NPASS - 1; pass >= 0; --pass) {
     const int tid = opaque_tid(), t = tid % C::T, grp = tid / C::T;
@@ -313,7 +380,7 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
     const int lo = pass_lo<C>(pass);
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
-    inv_stages<C, TWM>(x, t, lo, s1, s0, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u);
+    inv_stages<C, TWM>(x, t, lo, s1, s0, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u, wq);
     if (pass > 0) {
       const int lo2 = pass_lo<C>(pass - 1);
       if constexpr (C::CL) {
@@ -322,6 +389,7 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo))] = x[r];
+      if (tw_piped<C, TWM>(lo2, s0 - 1)) tw_fetch<C>(tw, t, lo2, s0 - 1, wq);
       grp_bar<C>(grp);
 #pragma unroll
       for (int r = 0; r < C::P; ++r) x[r] = buf[swz<C>(cbfft::elem_index<C::LOGP>(t, r, lo2))];
@@ -570,6 +638,14 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
                        (C::CL ? 0u : (u32)r * C::POLY_BLOCK_BYTES);
       constexpr u32 KEY_RR_STRIDE = (u32)GS * C::POLY_BLOCK_BYTES;
       const u32 sib = smem_u32(smem) + (u32)(ct * GS) * C::BUF_BYTES + (u32)t * 16;
+      constexpr bool PIPE = V4_PROD_PIPE && !C::CL;
+      u32 pk_key[GS], pk_f[GS];
+#pragma unroll
+      for (int j = 0; j < GS; ++j) {
+        const u32 rr = (u32)(r + j) % (u32)GS;
+        pk_key[j] = rr * KEY_RR_STRIDE;
+        pk_f[j] = sib + rr * C::BUF_BYTES;
+      }
       // cluster variant: the partners' buffers through distributed shared memory, fetched one
       // ring block ahead of their use (a remote load takes ~200 cycles)
       // (partner j of this CTA is the CTA of rank (r + 1 + j) mod (k+1))
@@ -611,6 +687,22 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
                              : "r"(sib_cl[j] + (u32)(((b + 1) * C::RB + pr) * T * 16)));
           }
         }
+        // V4_PROD_PIPE: (key, partner transform) operands of the current and of the next row; slot j is
+        // polynomial (r + j) mod (k+1), j = 0 the own term (operand x[p], key only)
+        double2 wc[GS], fc[GS], wn[GS], fn2[GS];
+        auto load_row = [&](int pr, double2(&w)[GS], double2(&f)[GS]) {
+#pragma unroll
+          for (int j = 0; j < GS; ++j) {
+            asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                         : "=d"(w[j].x), "=d"(w[j].y)
+                         : "r"(slot + pk_key[j] + (u32)pr * C::ROW_BYTES));
+            if (j > 0)
+              asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];"
+                           : "=d"(f[j].x), "=d"(f[j].y)
+                           : "r"(pk_f[j] + (u32)((b * C::RB + pr) * T * 16)));
+          }
+        };
+        if constexpr (PIPE) load_row(0, wc, fc);
 #pragma unroll
         for (int pr = 0; pr < C::RB; ++pr) {
           const int p = b * C::RB + pr;
@@ -640,6 +732,22 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
               const double2 f = fs[j][pr];
               o.x = fma(f.x, w.x, fma(-f.y, w.y, o.x));
               o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
+            }
+          } else if constexpr (PIPE) {
+            if (pr + 1 < C::RB) load_row(pr + 1, wn, fn2);
+            o.x = fma(x[p].x, wc[0].x, fma(-x[p].y, wc[0].y, o.x));
+            o.y = fma(x[p].x, wc[0].y, fma(x[p].y, wc[0].x, o.y));
+#pragma unroll
+            for (int j = 1; j < GS; ++j) {
+              o.x = fma(fc[j].x, wc[j].x, fma(-fc[j].y, wc[j].y, o.x));
+              o.y = fma(fc[j].x, wc[j].y, fma(fc[j].y, wc[j].x, o.y));
+            }
+            if (pr + 1 < C::RB) {
+#pragma unroll
+              for (int j = 0; j < GS; ++j) {
+                wc[j] = wn[j];
+                fc[j] = fn2[j];
+              }
             }
           } else {
 #pragma unroll

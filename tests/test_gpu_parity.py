@@ -346,6 +346,21 @@ def test_pbs_v4_cluster_rounds_and_tail(engine):
     _pbs_check(engine, ks, 74 * 2 + 29, 4, use_ks=False)
 
 
+@pytest.mark.parametrize("num", [296, 297, 741 + 148 * 5])
+def test_pbs_k2_batch_size_picks_kernel(engine, num):
+    """k = 2, N = 1024 (P4): ONE converted key, two kernels - up to 296 samples the group kernel
+    reads the v4 key layout (pbs_grp.cuh FOLD = 1), from 297 on the v4 kernel (one warp per
+    polynomial, 5 ciphertexts per CTA) runs.  Both sides of the switch against the oracle."""
+    _pbs_check(engine, keyset("P4", n_override=8), num, 3, use_ks=False)
+
+
+@pytest.mark.parametrize("num", [9, 760])
+def test_pbs_k2_wide_states_both_kernels(engine, num):
+    """Same switch with base_log * level > 31 (64-bit decomposition states) and two levels."""
+    prm = TfheParams("K2_N1024_wide", 6, 2, 1024, 2, 17, 3, 4, 2, 2.0 ** -24, 2.0 ** -55)
+    _pbs_check(engine, KeySet(prm, seed=42), num, 2, use_ks=False)
+
+
 @pytest.mark.parametrize("name,n_small,num", [("P8", 12, 90), ("P7", 12, 160), ("P2048", 20, 900),
                                               ("P4", 16, 750)])
 def test_pbs_deterministic_and_families_agree(engine, name, n_small, num):
