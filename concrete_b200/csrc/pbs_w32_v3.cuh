@@ -28,6 +28,11 @@
 // Arithmetic is unchanged from v1/v2 (same transforms, same rounding, same digit extraction).
 #pragma once
 
+#ifndef W32_V3_L2_KEEP
+#define W32_V3_L2_KEEP 0 // 1 = key fills carry an L2 evict_last hint (sm100_prims.cuh tma_load_bulk_keep).
+                         // Measured (profiles/r2_l2_keep_ab.txt): DRAM reads 826.7 MB with, 824.0 MB
+                         // without, same time - the excess reads are not key evictions; off
+#endif
 #ifndef W32_V3_LF
 #define W32_V3_LF 1 // inverse pass 1 with 6-op butterflies (pbs_w32.cuh inv_pass1_lf); 0 = 8-op
 #endif
@@ -98,10 +103,17 @@ __device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
   unsigned char *dst = smem + V3_OFF_RING + slot * V3_SLOT_BYTES;
   // slot layout [r][own, cross]: polynomial (row r, column c) of the GGSW goes to position
   // 2r + (c != r), so a warp addresses both of its polynomials from one base register
+#if W32_V3_L2_KEEP
+  const unsigned long long pol = l2_policy_evict_last();
+#endif
 #pragma unroll
   for (int poly = 0; poly < 4; ++poly) {
     const int r = poly >> 1, c = poly & 1, pos = 2 * r + (c != r);
+#if W32_V3_L2_KEEP
+    tma_load_bulk_keep(dst + pos * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot], pol);
+#else
     tma_load_bulk(dst + pos * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot]);
+#endif
   }
 }
 

@@ -39,6 +39,24 @@ __device__ __forceinline__ void tma_load_bulk(void *dst_smem, const void *src_gm
       "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
+// Same copy with an L2 evict_last hint (per instruction: no device-wide persisting carve-out,
+// nothing to undo on the caller's stream).  Tried on the Fourier-key fills of the N = 2048 kernel
+// against its 3x excess of DRAM reads (820 MB per launch for 146 MB of compulsory reads): no
+// effect (profiles/r2_l2_keep_ab.txt), so the excess is not the key being evicted between rounds;
+// kept for experiments (W32_V3_L2_KEEP).
+__device__ __forceinline__ unsigned long long l2_policy_evict_last() {
+  unsigned long long pol;
+  asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ void tma_load_bulk_keep(void *dst_smem, const void *src_gmem, u32 bytes,
+                                                   unsigned long long *bar, unsigned long long pol) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, "
+      "[%3], %4;" ::"r"(smem_u32(dst_smem)),
+      "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)), "l"(pol)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st16(u32 taddr, const u32 (&v)[16]) {
   asm volatile(
       "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, "
