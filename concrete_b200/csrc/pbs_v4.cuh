@@ -36,6 +36,10 @@
 #define V4_PROD_PIPE 1 // product phase (non-cluster): key and partner loads of row p+1 issued before the
                        // FMAs of row p, own term first and no branch on the polynomial index; 0 = first form
 #endif
+#ifndef V4_SHFL_X
+#define V4_SHFL_X 1 // a last pass of ONE stage (M = 2^(LOGP*j + 1)) is reached by a lane-pair shuffle, not
+                    // through shared memory (shfl_exchange below); 0 = every exchange through shared memory
+#endif
 #ifndef V4_TW_CONST
 #define V4_TW_CONST 0 // 1 = warp-uniform twiddles of a non-first pass from the constant bank.  Measured at
                       // P8 x 1024: 625.6 ms against 626.4 ms from global memory - no effect, off
@@ -330,6 +334,51 @@ __device__ __forceinline__ void inv_stages(double2 (&x)[C::P], int t, int lo, in
   }
 }
 
+// ---- exchange by shuffle when the last pass has ONE stage --------------------------------------------
+// Layout lo = 1 (bits [1, LOGP] of the index in-thread, bit 0 = bit 0 of t) <-> layout lo = 0 (bits
+// [0, LOGP) in-thread): only index bit 0 and bit LOGP trade places, and both layouts keep bits
+// above LOGP in t >> 1 - the exchange is a swap of half of the points between the lanes t and
+// t ^ 1.  Forward (lo 1 -> 0): old slot r of lane parity h goes to lane parity r >> (LOGP-1), new
+// slot 2 (r mod P/2) + h; the inverse direction is the mirror.  No shared memory, no barrier:
+// N = 16384 (13 = 4 + 4 + 4 + 1 stages) saves three of its nine 2 x 128 KiB exchanges per CMUX,
+// k = 2 / N = 1024 (9 = 4 + 4 + 1) three of six.  Same values in the same registers as the
+// shared-memory exchange: results are bit-identical.
+template <class C> struct ShX {
+  static constexpr int LAST_G = C::LOGM - C::LOGP * (C::NPASS - 1);
+  static constexpr bool ON = V4_SHFL_X && C::NPASS >= 2 && LAST_G == 1 && C::LOGP >= 2;
+};
+__device__ __forceinline__ double2 shfl_xor1(const double2 v) {
+  return make_double2(__shfl_xor_sync(0xffffffffu, v.x, 1), __shfl_xor_sync(0xffffffffu, v.y, 1));
+}
+template <class C> __device__ __forceinline__ void shfl_exchange_fwd(double2 (&x)[C::P], int t) {
+  constexpr int H = C::P / 2;
+  const bool h = t & 1;
+  double2 y[C::P];
+#pragma unroll
+  for (int m = 0; m < H; ++m) {
+    const double2 a = x[m], b = x[H + m];
+    const double2 keep = h ? b : a, recv = shfl_xor1(h ? a : b);
+    y[2 * m] = h ? recv : keep;
+    y[2 * m + 1] = h ? keep : recv;
+  }
+#pragma unroll
+  for (int r = 0; r < C::P; ++r) x[r] = y[r];
+}
+template <class C> __device__ __forceinline__ void shfl_exchange_inv(double2 (&x)[C::P], int t) {
+  constexpr int H = C::P / 2;
+  const bool h = t & 1;
+  double2 y[C::P];
+#pragma unroll
+  for (int m = 0; m < H; ++m) {
+    const double2 a = x[2 * m], b = x[2 * m + 1];
+    const double2 keep = h ? b : a, recv = shfl_xor1(h ? a : b);
+    y[m] = h ? recv : keep;
+    y[H + m] = h ? keep : recv;
+  }
+#pragma unroll
+  for (int r = 0; r < C::P; ++r) x[r] = y[r];
+}
+
 // In: x[r] = z_{t + r*T}.  Out: x[r] = F_{q = t*P + r}.  Every exchange is barrier / write /
 // barrier / read, so the buffer may have other readers right up to the call.
 // `pending` (cluster variant): the partners may still be reading this CTA's buffer (their product
@@ -348,7 +397,13 @@ __device__ __forceinline__ void forward(double2 (&x)[C::P], const double2 *__res
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
     fwd_stages<C, TWM>(x, t, lo, s0, s1, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u, wq);
-    if (pass + 1 < C::NPASS) {
+    if (ShX<C>::ON && pass + 2 == C::NPASS) {
+      if constexpr (C::CL) { // (a two-pass transform has no shared-memory exchange to wait in front of)
+        if (pass == 0 && pending) cluster_wait();
+      }
+      shfl_exchange_fwd<C>(x, t);
+      if (tw_piped<C, TWM>(0, s1)) tw_fetch<C>(tw, t, 0, s1, wq);
+    } else if (pass + 1 < C::NPASS) {
       const int lo2 = pass_lo<C>(pass + 1);
       if constexpr (C::CL) {
         if (pass == 0 && pending) cluster_wait();
@@ -381,10 +436,19 @@ __device__ __forceinline__ void inverse(double2 (&x)[C::P], const double2 *__res
     const int s0 = pass * C::LOGP;
     const int s1 = (pass == C::NPASS - 1) ? C::LOGM : s0 + C::LOGP;
     inv_stages<C, TWM>(x, t, lo, s1, s0, tw, (TWM && pass > 0) ? tw_tmem<C>(pass) : 0u, wq);
-    if (pass > 0) {
+    // `pending`: the cluster barrier is waited for in front of the FIRST write to shared memory
+    constexpr int FIRST_SMEM_PASS = ShX<C>::ON ? C::NPASS - 2 : C::NPASS - 1;
+    if (ShX<C>::ON && pass == C::NPASS - 1) {
+      shfl_exchange_inv<C>(x, t);
+      const int lo2 = pass_lo<C>(pass - 1);
+      if (tw_piped<C, TWM>(lo2, s0 - 1)) tw_fetch<C>(tw, t, lo2, s0 - 1, wq);
+      if constexpr (C::CL) {
+        if (FIRST_SMEM_PASS == 0 && pending) cluster_wait(); // two-pass transform: nothing else waits
+      }
+    } else if (pass > 0) {
       const int lo2 = pass_lo<C>(pass - 1);
       if constexpr (C::CL) {
-        if (pass == C::NPASS - 1 && pending) cluster_wait();
+        if (pass == FIRST_SMEM_PASS && pending) cluster_wait();
       }
       grp_bar<C>(grp);
 #pragma unroll
