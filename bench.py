@@ -619,14 +619,18 @@ def run_ours(args):
         "kernel": "pbs_kernel (fused blind rotation + sample extraction)",
         "bound": "fp64", "achieved": achieved_tf, "peak": fp64_peak, "unit": "TFLOP/s",
         "frac": achieved_tf / fp64_peak,
+        # the same fraction with the separate-twist term (6 M per transform) left out of the
+        # numerator: the kernels never execute that pass (merged into the butterfly twiddles)
+        "frac_without_twist_term": (flops - S * p.n * (p.k + 1) * (p.l + 1) * 6 * (p.N // 2))
+                                   / (pbs_ms * 1e-3) / 1e12 / fp64_peak,
         "peak_source": "FP64 FMA peak measured live by concrete_b200_fp64_peak (of measured)",
         "flops_per_pbs": p.pbs_flops(), "launch_ms": pbs_ms,
         "flops_convention": "algorithmic count of SURVEY.md 8(d): per CMUX (k+1)(l+1) transforms of "
                             "5 M log2 M + 6 M flop (the 6 M twist term is counted although the kernels "
                             "merge the twist into the butterfly twiddles: ~10 % of the numerator at "
                             "N = 2048) + (k+1)^2 l M 8 flop of products; EXECUTED FP64 instructions are "
-                            "reported by ncu in profiles/ (P2048: 2867 per thread-CMUX for 2048 "
-                            "algorithmic FMA-equivalents)",
+                            "reported by ncu in profiles/ (P2048: 2720 FP64-pipe instructions per "
+                            "thread-CMUX for 2048 algorithmic FMA-equivalents)",
         "hbm": {"achieved": bytes_alg / (pbs_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                 "frac": bytes_alg / (pbs_ms * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
