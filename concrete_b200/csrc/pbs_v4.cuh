@@ -40,6 +40,10 @@
 #define V4_SHFL_X 1 // a last pass of ONE stage (M = 2^(LOGP*j + 1)) is reached by a lane-pair shuffle, not
                     // through shared memory (shfl_exchange below); 0 = every exchange through shared memory
 #endif
+#ifndef V4_ST_TMEM
+#define V4_ST_TMEM 1 // two levels, 32-bit states: the states wait out the first level's transform and product in
+                     // the (still empty) Fourier-accumulator columns of tensor memory instead of being spilled
+#endif
 #ifndef V4_TW_CONST
 #define V4_TW_CONST 0 // 1 = warp-uniform twiddles of a non-first pass from the constant bank.  Measured at
                       // P8 x 1024: 625.6 ms against 626.4 ms from global memory - no effect, off
@@ -597,6 +601,12 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
   // base_log <= 15 since 2 * base_log <= 31) is packed into ONE register, so 16 registers less
   // are live across the first forward transform and product (ptxas: 532 -> 128 B of spills)
   constexpr bool PACK2 = (LV == 2) && NARROW && C::PACK;
+  // ST_TM (two levels, 32-bit states, no packing): after the first level's digits the 2 P state words
+  // of a thread are parked in the first 2 P of the 4 P tensor-memory columns that will hold the
+  // Fourier accumulators of level 0 - those are written only after the level-0 product, right
+  // after the states have been read back.  ptxas spilled them instead (256 B of stores and 128 B
+  // of loads per thread and CMUX through a 28 KiB L1 next to 227 KiB of shared memory, i.e. L2).
+  constexpr bool ST_TM = V4_ST_TMEM && C::STASH && LV == 2 && NARROW && !PACK2 && (2 * P) % 16 == 0;
   // FAST1 (one level): closest_representable + the balanced digit straight from the HIGH word of
   // ct1 in two integer instructions (the rounding bit 63 - base_log lies in the high word for every
   // base_log <= 31; same derivation as pbs_w32_v3.cuh neg_digit_l1_k: round-half-up of x is minus
@@ -676,6 +686,24 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
       for (int p = 0; p < P; ++p) {
         x[p].x = __int2double_rn((int)(u32)grp_decompose<st_t>(st_re[p], mask, base_log));
         x[p].y = __int2double_rn((int)(u32)grp_decompose<st_t>(st_im[p], mask, base_log));
+      }
+      if constexpr (ST_TM) {
+        if (m == 0) {
+          const int warp = opaque_tid() >> 5;
+          const u32 tm_st = ctrl->tmem_base + ((u32)((warp & 3) * 32) << 16) +
+                            (u32)(warp >> 2) * C::TM_PER_WARP + C::TM_OWN;
+#pragma unroll
+          for (int c = 0; c < 2 * P / 16; ++c) {
+            u32 v[16];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              v[2 * e + 0] = (u32)st_re[8 * c + e];
+              v[2 * e + 1] = (u32)st_im[8 * c + e];
+            }
+            tmem_st16(tm_st + 16 * c, v);
+          }
+          tmem_wait_st();
+        }
       }
     }
     // its first barrier also ends the rotated reads of ACC; for m > 0 of the cluster variant the
@@ -846,6 +874,19 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
       // variant only ARRIVES here and waits behind the register stages of the next transform
       if constexpr (C::CL) cluster_arrive();
       else ct_bar<C>(ct);
+      if constexpr (ST_TM) { // states back (unconditionally: every path to the next level redefines them)
+#pragma unroll
+        for (int c = 0; c < 2 * P / 16; ++c) {
+          u32 v[16];
+          tmem_ld16(tm_stash + 16 * c, v);
+          tmem_wait_ld();
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            st_re[8 * c + e] = (st_t)v[2 * e + 0];
+            st_im[8 * c + e] = (st_t)v[2 * e + 1];
+          }
+        }
+      }
       if (C::STASH && m + 1 < level) {
 #pragma unroll
         for (int c4 = 0; c4 < P / 4; ++c4) {

@@ -355,9 +355,11 @@ def test_pbs_k2_batch_size_picks_kernel(engine, num):
 
 
 @pytest.mark.parametrize("num", [9, 760])
-def test_pbs_k2_wide_states_both_kernels(engine, num):
-    """Same switch with base_log * level > 31 (64-bit decomposition states) and two levels."""
-    prm = TfheParams("K2_N1024_wide", 6, 2, 1024, 2, 17, 3, 4, 2, 2.0 ** -24, 2.0 ** -55)
+@pytest.mark.parametrize("b", [17, 10])
+def test_pbs_k2_two_levels_both_kernels(engine, num, b):
+    """Same switch with two levels: base_log * level > 31 (64-bit decomposition states) and <= 31
+    (32-bit states, parked in tensor memory between the levels by the v4 kernel)."""
+    prm = TfheParams(f"K2_N1024_b{b}", 6, 2, 1024, 2, b, 3, 4, 2, 2.0 ** -24, 2.0 ** -55)
     _pbs_check(engine, KeySet(prm, seed=42), num, 2, use_ks=False)
 
 
