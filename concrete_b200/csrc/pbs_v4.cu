@@ -55,19 +55,17 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 16384) { // 128 + 96 KiB
-    v = make_v4<1, 14, 1, 2, 3, true>();
+    // 32 points per thread (8 warps, up to 255 registers, 5 + 5 + 3 stages: two exchanges per
+    // transform): with the decomposition states parked in tensor memory it is spill-free and
+    // measured 579.3 ms at P8 x 1024 against 602.3 ms for 16 points per thread (16 warps, 128
+    // registers, 4 + 4 + 4 + 1 stages with the last exchange by shuffle), which stays selectable:
+    // tuning hook 2 = 16 points per thread, 1 = the same with packed decomposition states.
     const int alt = g_v4_alt.load();
-    if (alt == 1) v.two_narrow = v4::pbs_kernel_v4<v4::Cfg<1, 14, 4, 1, true, 2, 3, true, true>, true, 2>;
-    if (alt == 2) { // 32 points per thread: 8 warps, 5 + 5 + 3 stages (two exchanges instead of three)
-      using C5 = v4::Cfg<1, 14, 5, 1, true, 4, 3, true>;
-      v.two_narrow = v4::pbs_kernel_v4<C5, true, 2>;
-      v.one_level = v.multi_narrow = v.multi_wide = nullptr;
-      v.convert = v4::bsk_convert_kernel_v4<C5>;
-      v.threads = C5::THREADS;
-      v.T = C5::T;
-      v.logp = 5;
-      v.smem = v.smem_stash = C5::SMEM;
-      v.convert_smem = C5::BUF_BYTES;
+    if (alt == 1 || alt == 2) {
+      v = make_v4<1, 14, 1, 2, 3, true>();
+      if (alt == 1) v.two_narrow = v4::pbs_kernel_v4<v4::Cfg<1, 14, 4, 1, true, 2, 3, true, true>, true, 2>;
+    } else {
+      v = make_v4<1, 14, 1, 4, 3, true, 5>();
     }
     return true;
   }

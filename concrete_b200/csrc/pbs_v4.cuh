@@ -167,6 +167,9 @@ template <class C> __device__ __forceinline__ int poly_of(int grp) {
 // each thread keeps its (NPASS - 1) * P/2 twiddles there (tcgen05.ld, 12 cycles) - the v3 device.
 // Slot of the twiddle of stage rho (in-thread bit paired) and block pair h >> 1 inside a pass:
 // rho = LOGP-1 -> 0; rho = LOGP-2 -> 1; rho <= LOGP-3 -> 2^(LOGP-rho-2) + (h >> 1).
+// (32 points per thread with 64 twiddle columns per pass was built and measured for N = 4096 / 8192 -
+// 8 warps, 255 registers, 5 + 5 + 1 / 5 + 5 + 2 stages - and lost to 16 points per thread: P6 x 4096
+// 167.0 against 150.3 ms, P7 x 4096 417.3 against 407.0 ms; profiles/r2_p32_one_level_ab.txt)
 template <class C> struct TwT {
   static constexpr int SLOTS = C::P / 2;
   static constexpr u32 PASS_COLS = (u32)SLOTS * 4;

@@ -288,11 +288,11 @@ uint64_t concrete_b200_kernel_launches(void);
  * tensor cores (tcgen05.mma kind::i8, TMEM accumulators) whenever exact. */
 void concrete_b200_set_pbs_plan(int plan);
 void concrete_b200_set_ks_plan(int plan);
-/* TUNING hook: alternative instantiations of v4 kernels, 0 = the default.  1: N = 16384 two-level
- * kernel with packed decomposition states (same key layout).  2: N = 16384 with 32 points per
- * thread, 3: k = 2, N = 1024 with 8 points per thread and 3 ciphertexts per CTA - these two change
- * the Fourier key layout, so set them BEFORE the key is converted (and with plan 4 for k = 2: the
- * automatic plan's small-batch kernel reads the default layout only). */
+/* TUNING hook: alternative instantiations of v4 kernels, 0 = the default.  N = 16384: 2 = 16 points
+ * per thread (the default has 32), 1 = the same with packed decomposition states.  k = 2, N = 1024:
+ * 3 = 8 points per thread and 3 ciphertexts per CTA.  All of them change the Fourier key layout, so
+ * set the hook BEFORE the key is converted (and with plan 4 for k = 2: the automatic plan's
+ * small-batch kernel reads the default layout only). */
 void concrete_b200_set_v4_alt(int alt);
 /* FP64 FMA peak probe: `blocks` CTAs x 256 threads x iters x 16 DFMA (32 flop) per thread;
  * bench.py times it with CUDA events for the roofline denominator. */

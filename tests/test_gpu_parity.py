@@ -324,12 +324,29 @@ def test_pbs_every_kernel_family(engine, name, n_small, plan):
 
 @pytest.mark.parametrize("k,N,b,l", [(1, 8192, 15, 2), (1, 1024, 12, 3), (1, 2048, 9, 3),
                                      (2, 1024, 10, 2), (1, 4096, 11, 2), (1, 2048, 16, 2),
-                                     (1, 16384, 15, 2), (1, 16384, 22, 1), (1, 16384, 11, 3)])
+                                     (1, 16384, 15, 2), (1, 16384, 22, 1), (1, 16384, 11, 3),
+                                     (1, 16384, 9, 3)])
 def test_pbs_v4_multi_level(engine, k, N, b, l):
     """v4 with l >= 2: Fourier accumulators parked in tensor memory between levels; 32-bit
     (b*l <= 31) and 64-bit (b*l > 31) decomposition states."""
     prm = TfheParams(f"V4_k{k}_N{N}_l{l}", 20, k, N, l, b, 3, 4, 2, 2.0 ** -24, 2.0 ** -55)
     _pbs_check(engine, KeySet(prm, seed=42), 13, 2, use_ks=False)
+
+
+@pytest.mark.parametrize("name,n_small,alt,plan,num", [("P8", 10, 2, 0, 80), ("P8", 10, 1, 0, 9),
+                                                       ("P4", 16, 3, 4, 450)])
+def test_pbs_v4_tuning_variants(engine, name, n_small, alt, plan, num):
+    """The instantiations behind concrete_b200_set_v4_alt stay correct: N = 16384 with 16 points per
+    thread (the default has 32; last exchange by shuffle) and with packed decomposition states,
+    k = 2 / N = 1024 with 8 points per thread.  Hook (and plan) are set before the key is converted:
+    these variants have their own Fourier key layout."""
+    engine.lib.concrete_b200_set_v4_alt(alt)
+    engine.lib.concrete_b200_set_pbs_plan(plan)
+    try:
+        _pbs_check(engine, keyset(name, n_override=n_small), num, 3, use_ks=False)
+    finally:
+        engine.lib.concrete_b200_set_v4_alt(0)
+        engine.lib.concrete_b200_set_pbs_plan(0)
 
 
 def test_pbs_v4_rounds_and_tail(engine):
