@@ -52,6 +52,8 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   // GGSW level are resident; the whole level where the shared memory left by the buffers allows
   if (k == 1 && N == 1024) { v = make_v4<1, 10, 8, 8, 2>(); return true; }  // 128 + 32 KiB
   if (k == 1 && N == 2048) { v = make_v4<1, 11, 4, 8, 2>(); return true; }  // 128 + 64 KiB
+  // (finer ring blocks - RB x NB = 2 x 6 at N = 4096, 1 x 6 at N = 8192 - measured 165.4 against 150.5 ms
+  // and 482.2 against 407.3 ms: every block costs a barrier wait and a counted hand-back per warp)
   if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 16384) { // 128 + 96 KiB
