@@ -20,7 +20,7 @@ dump pbs_kernel_w32v3 'pbs_kernel_w32v3'
 dump ks_umma_kernel 'ks_umma_kernel'
 dump pbs_kernel_v4_N8192 'pbs_kernel_v4INS_3CfgILi1ELi13ELi4ELi1ELb0.*ELb1ELi1EEE'
 dump pbs_kernel_v4_N4096 'pbs_kernel_v4INS_3CfgILi1ELi12ELi4ELi2ELb0.*ELb1ELi1EEE'
-dump pbs_kernel_v4_cluster_N16384 'pbs_kernel_v4INS_3CfgILi1ELi14ELi4ELi1ELb1ELi2ELi3ELb1ELb0EEELb1ELi2EEE'
+dump pbs_kernel_v4_cluster_N16384 'pbs_kernel_v4INS_3CfgILi1ELi14ELi5ELi1ELb1ELi4ELi3ELb1ELb0EEELb1ELi2EEE'
 dump pbs_kernel_v4_k2_N1024 'pbs_kernel_v4INS_3CfgILi2ELi10ELi4ELi5ELb0ELi8ELi2ELb0ELb0EEELb1ELi1EEE'
 dump pbs_kernel_grp_k2_N1024 'pbs_kernel_grpILi2ELi10ELb1ELi1'
 dump mask_fill_kernel 'mask_fill_kernel'
