@@ -73,11 +73,13 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   }
   if (k == 2 && N == 1024) {
     // 16 points per thread = one warp per polynomial (no named barrier inside a transform), 5
-    // ciphertexts per CTA, the whole GGSW resident in the ring (120 + 72 KiB): 191.8 ms at 16 384
-    // samples (P4) against 223.5 ms for the first configuration (8 points per thread, two warps per
-    // polynomial, 3 ciphertexts per CTA, 72 + 144 KiB), which stays behind the tuning hook.
+    // ciphertexts per CTA, the whole 72 KiB GGSW resident as ONE ring block (120 + 72 KiB): one
+    // barrier wait and one counted hand-back per CMUX, refilled while the CTA is busy with the
+    // inverse transform, phase A and the next forward transform.  P4 x 16 384: 179.5 ms; as two
+    // half-GGSW blocks 183.8 ms; the first configuration (8 points per thread, two warps per
+    // polynomial, 3 ciphertexts per CTA, 72 + 144 KiB), which stays behind tuning hook 3: 223.5 ms.
     // pbs.cu's group kernel reads this key layout too (FOLD = 1) and takes the small batches.
-    v = make_v4<2, 10, 5, 8, 2, false, 4>();
+    v = make_v4<2, 10, 5, 16, 1, false, 4>();
     if (g_v4_alt.load() == 3) v = make_v4<2, 10, 3, 4, 4, false, 3>();
     return true;
   }
