@@ -44,9 +44,25 @@ constexpr int NW3 = 2 * CPB3;           // warps per CTA
 constexpr int NTHREADS3 = 32 * NW3;     // 384
 constexpr u32 V3_BUF_BYTES = (u32)M * 16;                       // 16 KiB per warp
 constexpr u32 V3_OFF_RING = (u32)NW3 * V3_BUF_BYTES;            // 196 608
-constexpr int V3_SLOTS = 4;
-constexpr u32 V3_SLOT_BYTES = 8192;     // 4 Fourier rows (p = 4g..4g+3) of the 4 GGSW polynomials
-constexpr int V3_GROUPS = 8;            // groups of 4 rows per GGSW
+#ifndef W32_V3_GPF
+#define W32_V3_GPF 2 // compute groups (4 Fourier rows) per key fill: 2 = four 16 KiB fills per CMUX into two slots
+                     // (half the barrier waits and counted hand-backs), 1 = eight 8 KiB fills into four slots
+#endif
+constexpr int V3_GPF = W32_V3_GPF;
+constexpr int V3_GROUPS = 8;            // compute groups of 4 rows per GGSW
+constexpr int V3_FILLS = V3_GROUPS / V3_GPF;        // key fills per CMUX
+constexpr int V3_SLOTS = 4 / V3_GPF;                // ring slots (the ring stays 32 KiB)
+constexpr u32 V3_CH = 2048u * V3_GPF;   // bytes of one GGSW polynomial in a fill (4 * GPF rows x 32 lanes x 16 B)
+constexpr u32 V3_SLOT_BYTES = 4 * V3_CH; // the 4 GGSW polynomials
+static_assert(V3_GPF == 1 || V3_GPF == 2, "fills of 4 or 8 rows");
+// group G reads fill F = G / GPF of its CMUX (sub-block G % GPF of it): slot and mbarrier parity are
+// compile-time constants because every slot takes an even number of fills per CMUX
+template <int G> struct V3Fill {
+  static constexpr int F = G / V3_GPF, SUB = G % V3_GPF;
+  static constexpr int SLOT = F & (V3_SLOTS - 1), PARITY = (F / V3_SLOTS) & 1;
+  static constexpr bool FIRST = SUB == 0, LAST = SUB == V3_GPF - 1;
+};
+static_assert((V3_FILLS / V3_SLOTS) % 2 == 0, "static parity");
 constexpr u32 V3_OFF_CTRL = V3_OFF_RING + V3_SLOTS * V3_SLOT_BYTES;
 constexpr size_t SMEM_BYTES3 = V3_OFF_CTRL + 256;
 constexpr u32 V3_TMEM_COLS = 512;
@@ -91,7 +107,7 @@ __device__ __forceinline__ void sts128(u32 addr, const double2 v) {
   asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v.x), "d"(v.y) : "memory");
 }
 
-// Fill t = cmux * 8 + g: rows 4g..4g+3 of the four polynomials of GGSW i -> slot g & 3.
+// Fill t = cmux * FILLS + f: rows 4*GPF*f .. of the four polynomials of GGSW i -> slot f mod SLOTS.
 // One thread.  The caller has waited for empty[slot] of the previous fill.
 __device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
   extern __shared__ __align__(1024) unsigned char smem[];
@@ -99,7 +115,7 @@ __device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
   const u32 slot = g & (V3_SLOTS - 1);
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
   mbar_expect_tx(&ctrl->full_bar[slot], V3_SLOT_BYTES);
-  const double2 *src = ctrl->bsk + (size_t)i * 4 * M + (size_t)g * 4 * 32;
+  const double2 *src = ctrl->bsk + (size_t)i * 4 * M + (size_t)g * (4 * V3_GPF) * 32;
   unsigned char *dst = smem + V3_OFF_RING + slot * V3_SLOT_BYTES;
   // slot layout [r][own, cross]: polynomial (row r, column c) of the GGSW goes to position
   // 2r + (c != r), so a warp addresses both of its polynomials from one base register
@@ -110,9 +126,9 @@ __device__ __forceinline__ void v3_issue_fill(u32 i, u32 g) {
   for (int poly = 0; poly < 4; ++poly) {
     const int r = poly >> 1, c = poly & 1, pos = 2 * r + (c != r);
 #if W32_V3_L2_KEEP
-    tma_load_bulk_keep(dst + pos * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot], pol);
+    tma_load_bulk_keep(dst + pos * V3_CH, src + (size_t)poly * M, V3_CH, &ctrl->full_bar[slot], pol);
 #else
-    tma_load_bulk(dst + pos * 2048, src + (size_t)poly * M, 2048, &ctrl->full_bar[slot]);
+    tma_load_bulk(dst + pos * V3_CH, src + (size_t)poly * M, V3_CH, &ctrl->full_bar[slot]);
 #endif
   }
 }
@@ -128,35 +144,37 @@ template <int G> __device__ __forceinline__ u32 v3_try_full() {
       "selp.u32 %0, 1, 0, p;\n"
       "}\n"
       : "=r"(done)
-      : "r"(v3_ctrl_addr() + 8 * (G & (V3_SLOTS - 1))), "n"((G >> 2) & 1)
+      : "r"(v3_ctrl_addr() + 8 * V3Fill<G>::SLOT), "n"(V3Fill<G>::PARITY)
       : "memory");
   return done;
 }
 template <int G> __device__ __forceinline__ void v3_wait_full(u32 tried) {
-  if (!tried) mbar_wait_s(v3_ctrl_addr() + 8 * (G & (V3_SLOTS - 1)), (G >> 2) & 1);
+  if (V3Fill<G>::FIRST && !tried) mbar_wait_s(v3_ctrl_addr() + 8 * V3Fill<G>::SLOT, V3Fill<G>::PARITY);
 }
 // This warp has issued its last read of fill t0 + G: count it (shared-memory operations of a
 // warp execute in order, so the count follows the reads).  Returns the previous count to lane 0.
 template <int G> __device__ __forceinline__ u32 v3_count_done(int lane) {
   u32 old = 0;
+  if (!V3Fill<G>::LAST) return old; // more reads of this fill to come (the next group's)
   __syncwarp();
   if (lane == 0)
     asm volatile("atom.shared.inc.u32 %0, [%1], %2;" // wraps to 0 after the 12th warp
                  : "=r"(old)
-                 : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * (G & (V3_SLOTS - 1))), "n"(NW3 - 1)
+                 : "r"(v3_ctrl_addr() + 8 * V3_SLOTS + 4 * V3Fill<G>::SLOT), "n"(NW3 - 1)
                  : "memory");
   return old;
 }
-// The warp that counted last (all 12 done) refills the slot with the group 4 ahead.
+// The warp that counted last (all 12 done) refills the slot with the fill SLOTS ahead.
 template <int G> __device__ __forceinline__ void v3_refill(u32 old, int lane) {
   extern __shared__ __align__(1024) unsigned char smem[];
-  if (lane == 0 && old == NW3 - 1) {
+  constexpr int F = V3Fill<G>::F;
+  if (V3Fill<G>::LAST && lane == 0 && old == NW3 - 1) {
     V3Ctrl *ctrl = reinterpret_cast<V3Ctrl *>(smem + V3_OFF_CTRL);
     const u32 t0 = ctrl->wt0[threadIdx.x >> 5], i = ctrl->wi[threadIdx.x >> 5];
-    if (t0 + G + V3_SLOTS < ctrl->total_fills) {
+    if (t0 + F + V3_SLOTS < ctrl->total_fills) {
       const u32 n = ctrl->n;
       const u32 inext = (i + 1 == n) ? 0 : i + 1;
-      v3_issue_fill((G + V3_SLOTS >= V3_GROUPS) ? inext : i, (G + V3_SLOTS) & (V3_GROUPS - 1));
+      v3_issue_fill((F + V3_SLOTS >= V3_FILLS) ? inext : i, (F + V3_SLOTS) & (V3_FILLS - 1));
     }
   }
 }
@@ -381,7 +399,7 @@ template <int P> __device__ __forceinline__ void ld_row_all(const V3Addr &A, dou
 // product of row P with the staged key: cross term to the partner through buf, own term in place
 template <int P, u32 SO>
 __device__ __forceinline__ void v3_product(double2 (&x)[32], const V3Addr &A, u32 keyr) {
-  const double2 w = lds128o<SO + 512 * (P & 3)>(keyr), wo = lds128o<SO + 2048 + 512 * (P & 3)>(keyr);
+  const double2 w = lds128o<SO + 512 * (P & 3)>(keyr), wo = lds128o<SO + V3_CH + 512 * (P & 3)>(keyr);
   st_row<P>(A, cmul(x[P], wo));
   x[P] = cmul(x[P], w);
 }
@@ -416,14 +434,14 @@ __device__ __forceinline__ void v3_fwd_group(double2 (&x)[32], const V3Addr &A, 
     }
   }
   v3_wait_full<G>(0);
-  constexpr u32 so = (G & (V3_SLOTS - 1)) * V3_SLOT_BYTES;
+  constexpr u32 so = V3Fill<G>::SLOT * V3_SLOT_BYTES + V3Fill<G>::SUB * 2048u;
   u32 old = 0;
   v3_product<4 * G + 0, so>(x, A, keyr);
   v3_product<4 * G + 1, so>(x, A, keyr);
   v3_product<4 * G + 2, so>(x, A, keyr);
   {
     constexpr int p = 4 * G + 3;
-    const double2 w = lds128o<so + 512 * 3>(keyr), wo = lds128o<so + 2048 + 512 * 3>(keyr);
+    const double2 w = lds128o<so + 512 * 3>(keyr), wo = lds128o<so + V3_CH + 512 * 3>(keyr);
     old = v3_count_done<G>(lane); // every read of the slot has been issued
     st_row<p>(A, cmul(x[p], wo));
     x[p] = cmul(x[p], w);
@@ -529,7 +547,7 @@ __device__ __noinline__ void v3_cmux(const u32 a_hat) {
   __syncwarp(); // transpose reads of the buffer are done in every lane
   {
     const V3Phase P = v3_phase();
-    const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * P.lane + (P.warp & 1) * 4096;
+    const u32 key = smem_u32(smem) + V3_OFF_RING + 16u * P.lane + (P.warp & 1) * (2 * V3_CH);
     u32 ta[4], tb[4];
     tmem_ld4(P.tmem_tw + 16, ta);
     tmem_ld4(P.tmem_tw + 20, tb);
@@ -607,7 +625,7 @@ __global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a
   const u32 my_rem = rem_base + (blockIdx.x < rem_extra ? 1u : 0u);
   const u32 rem_first = full * wave + blockIdx.x * rem_base + min(blockIdx.x, rem_extra);
   const u32 rounds = full + (my_rem ? 1u : 0u);
-  const u32 total_fills = rounds * n * V3_GROUPS;
+  const u32 total_fills = rounds * n * V3_FILLS;
 
   if (tid == 0) {
 #pragma unroll
@@ -714,7 +732,7 @@ __global__ void __launch_bounds__(NTHREADS3, 1) pbs_kernel_w32v3(const PbsArgs a
       }
       const u32 a_hat = __shfl_sync(0xffffffffu, a_blk, i & 31);
       if (lane == 0) { // what the refill path needs to know about this warp's CMUX
-        ctrl->wt0[warp] = cmux * V3_GROUPS;
+        ctrl->wt0[warp] = cmux * V3_FILLS;
         ctrl->wi[warp] = i;
       }
       if (a_hat == 0) // X^0 - 1 = 0: no CMUX (bootstrap.rs:287); still walk the ring
