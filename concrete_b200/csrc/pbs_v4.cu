@@ -55,7 +55,11 @@ bool v4_variant(u32 k, u32 N, V4Variant &v) {
   // (finer ring blocks - RB x NB = 2 x 6 at N = 4096, 1 x 6 at N = 8192 - measured 165.4 against 150.5 ms
   // and 482.2 against 407.3 ms: every block costs a barrier wait and a counted hand-back per warp)
   if (k == 1 && N == 4096) { v = make_v4<1, 12, 2, 4, 3>(); return true; }  // 128 + 96 KiB
-  if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 2, 3>(); return true; }  // 128 + 96 KiB
+  // N = 8192: ring blocks of 3 rows in 2 slots of 48 KiB - six blocks per CMUX (5 x 3 + 1 rows; the block
+  // size need not divide the 16 rows) instead of eight blocks of 2 rows in 3 slots of 32 KiB: P7 x 4096
+  // 407.2 -> 389.1 ms.  The same 2 x 48 KiB geometry measured neutral at N = 4096 (6 + 6 + 4 rows: 150.4 ms
+  // either way) and at N = 16384 (5 x 6 + 2 rows per level: 581.1 against 579.5 ms), which keep 3 x 32 KiB.
+  if (k == 1 && N == 8192) { v = make_v4<1, 13, 1, 3, 2>(); return true; }  // 128 + 96 KiB
   if (k == 1 && N == 16384) { // 128 + 96 KiB
     // 32 points per thread (8 warps, up to 255 registers, 5 + 5 + 3 stages: two exchanges per
     // transform): with the decomposition states parked in tensor memory it is spill-free and

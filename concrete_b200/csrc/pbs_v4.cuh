@@ -77,7 +77,9 @@ struct Cfg {
   // ~90 cycles even when the data is there and the count is an atomic round trip, and with one of
   // each per row they were the critical path of the product (profiles/r2_v4a_*).  RB * NB rows is
   // what the shared memory left by the buffers holds: the whole level when it fits.
-  static constexpr int RB = RB_, NB = NB_, BLOCKS_PER_LEVEL = P / RB_;
+  // RB need not divide P: the last block of a level then has LAST_ROWS < RB rows (same slot stride)
+  static constexpr int RB = RB_, NB = NB_, BLOCKS_PER_LEVEL = (P + RB_ - 1) / RB_;
+  static constexpr int LAST_ROWS = P - (BLOCKS_PER_LEVEL - 1) * RB_;
   static constexpr u32 POLY_BLOCK_BYTES = (u32)RB_ * ROW_BYTES;         // RB rows of one polynomial
   static constexpr u32 BLOCK_BYTES = (u32)KEY_POLYS * POLY_BLOCK_BYTES; // RB rows of one level
   static constexpr u32 OFF_RING = (u32)GROUPS * BUF_BYTES;
@@ -89,7 +91,7 @@ struct Cfg {
   static_assert(T >= 32 && T % 32 == 0, "a group is a whole number of warps");
   static_assert(THREADS <= 1024 && THREADS % 32 == 0, "CTA size");
   static_assert(((NWARPS + 3) / 4) * TM_PER_WARP <= 512, "TMEM columns");
-  static_assert(P % RB_ == 0 && NB_ >= 1 && NB_ <= 16, "ring shape");
+  static_assert(RB_ >= 1 && RB_ <= P && NB_ >= 1 && NB_ <= 16, "ring shape");
   static_assert(SMEM <= 232448, "shared memory");
   static_assert(T == 32 || CPB_ + GROUPS <= 15, "named barriers");
   static_assert(!CL_ || CPB_ == 1, "cluster variant: one ciphertext per cluster");
@@ -478,7 +480,8 @@ template <class C> __device__ __noinline__ void issue_block(u32 i, u32 m, u32 b,
   const double2 *bsk = ctrl->bsk;
   const u32 level = ctrl->level;
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); // generic reads before async write
-  mbar_expect_tx(&ctrl->full_bar[slot], C::BLOCK_BYTES);
+  const u32 poly_bytes = (b + 1 == (u32)C::BLOCKS_PER_LEVEL ? (u32)C::LAST_ROWS : (u32)C::RB) * C::ROW_BYTES;
+  mbar_expect_tx(&ctrl->full_bar[slot], (u32)C::KEY_POLYS * poly_bytes);
   // cluster variant: this CTA consumes column r only: key polynomials (rr, r), rr = 0..k
   const size_t col = C::CL ? (size_t)cluster_rank() : 0, pstride = C::CL ? C::GS : 1;
   const double2 *src = bsk + (((size_t)i * level + m) * C::GS * C::GS + col) * C::M +
@@ -486,8 +489,8 @@ template <class C> __device__ __noinline__ void issue_block(u32 i, u32 m, u32 b,
   unsigned char *dst = smem + C::OFF_RING + slot * C::BLOCK_BYTES;
 #pragma unroll
   for (int poly = 0; poly < C::KEY_POLYS; ++poly)
-    tma_load_bulk(dst + poly * C::POLY_BLOCK_BYTES, src + (size_t)poly * pstride * C::M,
-                  C::POLY_BLOCK_BYTES, &ctrl->full_bar[slot]);
+    tma_load_bulk(dst + poly * C::POLY_BLOCK_BYTES, src + (size_t)poly * pstride * C::M, poly_bytes,
+                  &ctrl->full_bar[slot]);
   // Keys that do not fit the 126 MB L2 (N >= 4096: 115 MB .. 240 MB): all CTAs walk the GGSW index
   // together, so ONE early request per block turns every later fill into an L2 hit.  An eighth of
   // the CTAs asks for the same block two GGSWs ahead.
@@ -497,7 +500,7 @@ template <class C> __device__ __noinline__ void issue_block(u32 i, u32 m, u32 b,
     for (int poly = 0; poly < C::KEY_POLYS; ++poly)
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(ahead +
                                                                        (size_t)poly * pstride * C::M),
-                   "n"(C::POLY_BLOCK_BYTES)
+                   "r"(poly_bytes)
                    : "memory");
   }
 }
@@ -776,10 +779,12 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
 #pragma unroll
             for (int j = 0; j < NSIB; ++j)
 #pragma unroll
-              for (int pr = 0; pr < C::RB; ++pr)
+              for (int pr = 0; pr < C::RB; ++pr) {
+                if ((b + 1) * C::RB + pr >= P) continue; // short last block
                 asm volatile("ld.shared::cluster.v2.f64 {%0, %1}, [%2];"
                              : "=d"(fn[j][pr].x), "=d"(fn[j][pr].y)
                              : "r"(sib_cl[j] + (u32)(((b + 1) * C::RB + pr) * T * 16)));
+              }
           }
         }
         // V4_PROD_PIPE: (key, partner transform) operands of the current and of the next row; slot j is
@@ -801,6 +806,8 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
 #pragma unroll
         for (int pr = 0; pr < C::RB; ++pr) {
           const int p = b * C::RB + pr;
+          if (p >= P) continue; // short last block (RB does not divide P)
+          const bool more_rows = pr + 1 < C::RB && p + 1 < P;
           double2 o = make_double2(0.0, 0.0);
           if (C::STASH && m > 0) {
             u32 v[4];
@@ -829,7 +836,7 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
               o.y = fma(f.x, w.y, fma(f.y, w.x, o.y));
             }
           } else if constexpr (PIPE) {
-            if (pr + 1 < C::RB) load_row(pr + 1, wn, fn2);
+            if (more_rows) load_row(pr + 1, wn, fn2);
             o.x = fma(x[p].x, wc[0].x, fma(-x[p].y, wc[0].y, o.x));
             o.y = fma(x[p].x, wc[0].y, fma(x[p].y, wc[0].x, o.y));
 #pragma unroll
@@ -837,7 +844,7 @@ __device__ __noinline__ void cmux(const u32 a_hat, const u32 i, const u32 blk0) 
               o.x = fma(fc[j].x, wc[j].x, fma(-fc[j].y, wc[j].y, o.x));
               o.y = fma(fc[j].x, wc[j].y, fma(fc[j].y, wc[j].x, o.y));
             }
-            if (pr + 1 < C::RB) {
+            if (more_rows) {
 #pragma unroll
               for (int j = 0; j < GS; ++j) {
                 wc[j] = wn[j];
